@@ -1,0 +1,42 @@
+"""Loaders for the committed fixtures under tests/golden/ (generated from the reference build by
+tests/golden/make_golden.py).  Test infrastructure only."""
+import os
+
+import numpy as np
+
+GDIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+_cache = {}
+
+
+def _npz(name):
+    if name not in _cache:
+        _cache[name] = np.load(os.path.join(GDIR, name))
+    return _cache[name]
+
+
+def load_quant_tables():
+    """{(bd, plane): int16[256][5][8]} = zbin, round, quant, quant_shift, dequant rows of
+    av1_build_quantizer (all delta_q = 0)."""
+    z = _npz("quant_tables.npz")
+    return {(bd, pl): z[f"bd{bd}_p{pl}"] for bd in (8, 10) for pl in (0, 1, 2)}
+
+
+def load_scans():
+    """{(tx_size, scan_class): (scan int16[n], iscan int16[n])} from av1_scan_orders."""
+    z = _npz("scans.npz")
+    return {(s, c): (z[f"scan_{s}_{c}"], z[f"iscan_{s}_{c}"]) for s in range(19) for c in range(3)}
+
+
+def load_qmatrices():
+    """{(level, plane>=1, tx_size): (wt uint8[n], iwt uint8[n])} for the levels in the fixture."""
+    z = _npz("qmatrix.npz")
+    out = {}
+    for k in z.files:
+        if k.startswith("wt_"):
+            _, lv, pl, s = k.split("_")
+            out[(int(lv), int(pl), int(s))] = (z[k], z["i" + k])
+    return out
+
+
+def load_fused_vectors():
+    return _npz("fused_vectors.npz")

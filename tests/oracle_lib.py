@@ -1,0 +1,104 @@
+"""ctypes bindings for the CHECKERS (test infrastructure only):
+
+* ``oracle()``  -> oracle/libsvt_oracle.so, our plain-C restatement (always buildable: gcc only)
+* ``ref()``     -> oracle/_ref/libsvtref.so, the reference itself compiled from /root/reference
+                   (present in the build container and, as a prebuilt file, on the GPU box;
+                   ``None`` when it was never built)
+
+Nothing in the product package imports this module.
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ODIR = os.path.join(ROOT, "oracle")
+
+TX_W = [4, 8, 16, 32, 64, 4, 8, 8, 16, 16, 32, 32, 64, 4, 16, 8, 32, 16, 64]
+TX_H = [4, 8, 16, 32, 64, 8, 4, 16, 8, 32, 16, 64, 32, 16, 4, 32, 8, 64, 16]
+TX_NAMES = ["4X4", "8X8", "16X16", "32X32", "64X64", "4X8", "8X4", "8X16", "16X8", "16X32",
+            "32X16", "32X64", "64X32", "4X16", "16X4", "8X32", "32X8", "16X64", "64X16"]
+
+
+def P(a):
+    return a.ctypes.data_as(ctypes.c_void_p) if a is not None else None
+
+
+class SvtoBlock(ctypes.Structure):
+    _fields_ = [("tx_size", ctypes.c_uint8), ("tx_type", ctypes.c_uint8), ("bd", ctypes.c_uint8),
+                ("plane", ctypes.c_uint8), ("res_off", ctypes.c_uint32),
+                ("res_stride", ctypes.c_uint32), ("rec_off", ctypes.c_uint32),
+                ("rec_stride", ctypes.c_uint32), ("coeff_off", ctypes.c_uint32),
+                ("qrow", ctypes.c_uint32), ("flags", ctypes.c_uint32)]
+
+
+BLOCK_DTYPE = np.dtype([("tx_size", "u1"), ("tx_type", "u1"), ("bd", "u1"), ("plane", "u1"),
+                        ("res_off", "<u4"), ("res_stride", "<u4"), ("rec_off", "<u4"),
+                        ("rec_stride", "<u4"), ("coeff_off", "<u4"), ("qrow", "<u4"), ("flags", "<u4")])
+assert BLOCK_DTYPE.itemsize == ctypes.sizeof(SvtoBlock) == 32
+
+_oracle = None
+_ref = None
+
+
+def oracle():
+    global _oracle
+    if _oracle is None:
+        so = os.path.join(ODIR, "libsvt_oracle.so")
+        src = os.path.join(ODIR, "svt_oracle.c")
+        if not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+            subprocess.check_call(["make", "-s", "-C", ODIR, "oracle"])
+        _oracle = ctypes.CDLL(so)
+        _oracle.svto_cospi.restype = ctypes.POINTER(ctypes.c_int32)
+        _oracle.svto_sinpi.restype = ctypes.POINTER(ctypes.c_int32)
+    return _oracle
+
+
+def ref(asm=1):
+    """The compiled reference, or None.  asm=1: the AVX2 RTCD table (what the encoder runs)."""
+    global _ref
+    if _ref is None:
+        so = os.path.join(ODIR, "_ref", "libsvtref.so")
+        if not os.path.exists(so):
+            return None
+        _ref = ctypes.CDLL(so)
+    _ref.ref_init(int(asm))
+    return _ref
+
+
+def valid_pairs():
+    o = oracle()
+    return [(s, t) for s in range(19) for t in range(16) if o.svto_is_valid(s, t)]
+
+
+def max_eob(s):
+    return min(TX_W[s], 32) * min(TX_H[s], 32)
+
+
+def tx_scale(s):
+    pels = TX_W[s] * TX_H[s]
+    return int(pels > 256) + int(pels > 1024)
+
+
+def scan_class(t):
+    return 0 if t < 10 else (2 if t & 1 else 1)
+
+
+def aligned(shape, dtype, fill=0, align=64):
+    """numpy array whose data pointer is `align`-byte aligned (the reference's AVX2 kernels use
+    aligned 256-bit stores on their coefficient buffers)."""
+    dtype = np.dtype(dtype)
+    n = int(np.prod(shape))
+    raw = np.zeros(n * dtype.itemsize + align, np.uint8)
+    off = (-raw.ctypes.data) % align
+    a = raw[off:off + n * dtype.itemsize].view(dtype).reshape(shape)
+    a[...] = fill
+    return a
+
+
+def aligned_copy(x, align=64):
+    a = aligned(x.shape, x.dtype, align=align)
+    a[...] = x
+    return a
