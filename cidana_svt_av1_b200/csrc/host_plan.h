@@ -1,0 +1,108 @@
+// Host-side logic of libsvtgpu that needs no CUDA: scan-table generation, block validation and
+// bucketing.  Header-only so the CPU-only tests can exercise it (tests/host_emul.cpp).
+#pragma once
+#include <stdint.h>
+#include <vector>
+#include "../../include/svt_gpu.h"
+#include "residual_kernel.cuh"
+
+namespace svt {
+
+static const int kTxW[19] = { 4, 8, 16, 32, 64, 4, 8, 8, 16, 16, 32, 32, 64, 4, 16, 8, 32, 16, 64 };
+static const int kTxH[19] = { 4, 8, 16, 32, 64, 8, 4, 16, 8, 32, 16, 64, 32, 16, 4, 32, 8, 64, 16 };
+
+inline int coded_w(int s) { return kTxW[s] > 32 ? 32 : kTxW[s]; }
+inline int coded_h(int s) { return kTxH[s] > 32 ? 32 : kTxH[s]; }
+inline int max_eob(int s) { return coded_w(s) * coded_h(s); }  // av1_get_max_eob, EbTransforms.h:3872
+
+// is_txfm_allowed (AV1 5.11; reference test/TxfmCommon.h:172)
+inline bool tx_pair_valid(int s, int t) {
+    if (s < 0 || s > 18 || t < 0 || t > 15) return false;
+    const int m = kTxW[s] > kTxH[s] ? kTxW[s] : kTxH[s];
+    if (m == 64) return t == 0;
+    if (m == 32) return t == 0 || t == 9;
+    return true;
+}
+
+// Scan order of the coded region (kw x kh, 64-point sizes use their 32-wide counterpart), as a
+// rule instead of the reference's literal tables (EbTransforms.h:331-3348, selected by
+// av1_scan_orders :3349): class 1 "mrow" is raster order, class 2 "mcol" is column-major, class 0
+// walks the anti-diagonals -- always top-right to bottom-left for tall blocks, always bottom-left
+// to top-right for wide blocks, and alternating (odd diagonals downwards) for squares.
+inline void make_scan(int s, int cls, std::vector<int16_t>& scan) {
+    const int kw = coded_w(s), kh = coded_h(s);
+    scan.clear();
+    if (cls == 1) {
+        for (int i = 0; i < kw * kh; ++i) scan.push_back(int16_t(i));
+    } else if (cls == 2) {
+        for (int c = 0; c < kw; ++c)
+            for (int r = 0; r < kh; ++r) scan.push_back(int16_t(r * kw + c));
+    } else {
+        for (int d = 0; d < kw + kh - 1; ++d) {
+            const bool down = kh > kw ? true : (kw > kh ? false : (d & 1));
+            const int r_lo = d - (kw - 1) > 0 ? d - (kw - 1) : 0;
+            const int r_hi = d < kh - 1 ? d : kh - 1;
+            if (down) for (int r = r_lo; r <= r_hi; ++r) scan.push_back(int16_t(r * kw + (d - r)));
+            else      for (int r = r_hi; r >= r_lo; --r) scan.push_back(int16_t(r * kw + (d - r)));
+        }
+    }
+}
+inline void make_iscan(int s, int cls, std::vector<int16_t>& iscan) {
+    std::vector<int16_t> scan;
+    make_scan(s, cls, scan);
+    iscan.assign(scan.size(), 0);
+    for (size_t i = 0; i < scan.size(); ++i) iscan[scan[i]] = int16_t(i);
+}
+// all 19 x 3 tables back to back (sizes that share a coded shape share a table)
+inline void build_iscan_tables(std::vector<int16_t>& all, int off[19][3]) {
+    all.clear();
+    for (int s = 0; s < 19; ++s)
+        for (int c = 0; c < 3; ++c) {
+            int share = -1;
+            for (int s2 = 0; s2 < s; ++s2)
+                if (coded_w(s2) == coded_w(s) && coded_h(s2) == coded_h(s)) { share = s2; break; }
+            if (share >= 0) { off[s][c] = off[share][c]; continue; }
+            std::vector<int16_t> t;
+            make_iscan(s, c, t);
+            off[s][c] = int(all.size());
+            all.insert(all.end(), t.begin(), t.end());
+        }
+}
+
+// Validates the caller's list and buckets it by (tx_size, tx_type); stable inside a bucket so that
+// spatially adjacent blocks stay adjacent.  Returns 0 or the 1-based index of the first bad block.
+inline int bucket_blocks(const SvtGpuBlock* in, int n, std::vector<DevBlock>& out, int first[19],
+                         int count[19]) {
+    int hist[19][16] = {};
+    for (int i = 0; i < n; ++i) {
+        const SvtGpuBlock& b = in[i];
+        if (!tx_pair_valid(b.tx_size, b.tx_type)) return i + 1;
+        if (b.bit_depth != 8 && b.bit_depth != 10) return i + 1;
+        if (b.coeff_off & 3) return i + 1;
+        if (b.plane > 2) return i + 1;
+        ++hist[b.tx_size][b.tx_type];
+    }
+    int start[19][16];
+    int acc = 0;
+    for (int s = 0; s < 19; ++s) {
+        first[s] = acc;
+        for (int t = 0; t < 16; ++t) { start[s][t] = acc; acc += hist[s][t]; }
+        count[s] = acc - first[s];
+    }
+    out.resize(n);
+    for (int i = 0; i < n; ++i) {
+        const SvtGpuBlock& b = in[i];
+        DevBlock d;
+        d.res_off = b.res_off; d.res_stride = b.res_stride;
+        d.rec_off = b.rec_off; d.rec_stride = b.rec_stride;
+        d.coeff_off = b.coeff_off; d.qrow = b.qrow; d.id = uint32_t(i);
+        d.meta = uint32_t(b.tx_type) | (b.bit_depth == 10 ? META_BD10 : 0u) |
+                 (uint32_t(b.plane) << META_PLANE_SHIFT) |
+                 ((b.flags & SVTGPU_BLK_CLAMP16) ? META_CLAMP16 : 0u) |
+                 ((b.flags & SVTGPU_BLK_USE_QM) ? META_USE_QM : 0u);
+        out[start[b.tx_size][b.tx_type]++] = d;
+    }
+    return 0;
+}
+
+}  // namespace svt

@@ -1,0 +1,206 @@
+/*
+ * svt_gpu.h -- C ABI of libsvtgpu.so: the B200 (sm_100a) implementation of SVT-AV1's
+ * residual-coding path (forward 2-D transform, quantize/dequantize/eob, inverse transform +
+ * reconstruction).  Plain pointers and sizes only; no CUDA or torch types appear here.
+ *
+ * Three levels, mirroring SURVEY.md 8b.  Reference paths are relative to
+ * Source/Lib/Common/Codec/ of Cidana-SVT-AV1.
+ *
+ *   C. batch API (svtgpu_create .. svtgpu_run)  -- device-resident, asynchronous, what a batched
+ *      caller and the benchmarks use; one call = every transform block of a frame batch.
+ *   B. entry points  svtgpu_av1_estimate_transform / svtgpu_av1_quantize_inv_quantize /
+ *      svtgpu_av1_inv_transform_recon[8bit] -- same arguments as EbTransforms.h:3896-3987 minus
+ *      the PictureControlSet (the five quantizer table rows are passed instead); host pointers,
+ *      synchronous.
+ *   A. RTCD slots  svtgpu_av1_fwd_txfm2d_WxH, svtgpu_aom_[highbd_]quantize_b[_32x32|_64x64],
+ *      svtgpu_av1_inv_txfm2d_add_WxH, svtgpu_av1_inv_txfm_add -- byte-for-byte the prototypes of
+ *      the function pointers at aom_dsp_rtcd.h:158-255, 321-342, 347-423, so that
+ *      `av1_fwd_txfm2d_8x8 = svtgpu_av1_fwd_txfm2d_8x8;` compiles in the reference.  Host
+ *      pointers, synchronous, re-entrant (thread-local staging), void return: a CUDA failure
+ *      prints and abort()s -- there is no CPU fallback.
+ *
+ * TxType / TxSize are 1-byte packed enums in the reference (EbDefinitions.h:621, :728), hence
+ * uint8_t below.
+ */
+#ifndef SVT_GPU_H
+#define SVT_GPU_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------------------------------ */
+/* Level C: batch API                                                                          */
+/* ------------------------------------------------------------------------------------------ */
+typedef struct SvtGpuContext SvtGpuContext;
+typedef struct SvtGpuPlan SvtGpuPlan;
+
+enum { SVTGPU_OK = 0, SVTGPU_ERR_ARG = -1, SVTGPU_ERR_CUDA = -2, SVTGPU_ERR_NOMEM = -3 };
+enum { SVTGPU_STAGE_FWD = 1, SVTGPU_STAGE_QUANT = 2, SVTGPU_STAGE_INV = 4, SVTGPU_STAGE_ALL = 7 };
+enum { SVTGPU_BLK_CLAMP16 = 1, /* 8-bit C quantizer variant, EbFullLoop.c:86-88 */
+       SVTGPU_BLK_USE_QM = 2 /* quantization matrices, EbFullLoop.c:239-296 */ };
+
+/* One transform block.  Offsets index the batch-wide arrays of SvtGpuBuffers. */
+typedef struct SvtGpuBlock {
+    uint8_t tx_size;     /* TxSize 0..18 */
+    uint8_t tx_type;     /* TxType 0..15; must be legal for tx_size (AV1 5.11) */
+    uint8_t bit_depth;   /* 8 or 10 */
+    uint8_t plane;       /* 0 Y, 1 U, 2 V (selects the qmatrix set) */
+    uint32_t res_off;    /* int16 elements into residual */
+    uint32_t res_stride; /* int16 elements */
+    uint32_t rec_off;    /* pixels into pred / recon */
+    uint32_t rec_stride; /* pixels */
+    uint32_t coeff_off;  /* int32 elements into coeff / qcoeff / dqcoeff; multiple of 4 */
+    uint32_t qrow;       /* row of the uploaded quantizer tables */
+    uint32_t flags;      /* SVTGPU_BLK_* */
+} SvtGpuBlock;
+
+/* Device pointers (from svtgpu_malloc or any CUDA allocation of the same device). */
+typedef struct SvtGpuBuffers {
+    const int16_t *residual; /* STAGE_FWD input */
+    const void *pred;        /* STAGE_INV input: uint8 (bd 8) / uint16 (bd 10) pixels */
+    void *recon;             /* STAGE_INV output; may equal pred (in place, like the reference) */
+    const int32_t *coeff_in; /* input of QUANT / INV when STAGE_FWD is not requested */
+    int32_t *coeff;          /* optional output: transform coefficients, packed to min(w,32) */
+    int32_t *qcoeff;         /* STAGE_QUANT outputs */
+    int32_t *dqcoeff;
+    uint16_t *eob;           /* [n_blocks], indexed like the caller's block list */
+    uint64_t *energy;        /* [n_blocks] three_quad_energy (0 unless a 64-point size) */
+} SvtGpuBuffers;
+
+int svtgpu_create(SvtGpuContext **ctx, int device);
+void svtgpu_destroy(SvtGpuContext *ctx);
+const char *svtgpu_last_error(void);
+
+/* tables[n_rows][5][8] int16: zbin, round, quant, quant_shift, dequant rows exactly as
+ * av1_build_quantizer lays them out (EbModeDecisionConfigurationProcess.c:429; [0] DC, [1..7] AC) */
+int svtgpu_upload_quant_tables(SvtGpuContext *ctx, const int16_t *tables, int n_rows);
+/* wt/iwt: concatenated qmatrix arrays; off[plane>0][tx_size] = start of that size's matrix or -1
+ * (what av1_qm_init binds into gqmatrix/giqmatrix, :524-554) */
+int svtgpu_upload_qmatrix(SvtGpuContext *ctx, const uint8_t *wt, const uint8_t *iwt, int n_bytes,
+                          const int32_t *off /* [2][19] */);
+
+/* Validates and buckets the block list by (tx_size, tx_type) and keeps it on the device. */
+int svtgpu_plan_create(SvtGpuContext *ctx, const SvtGpuBlock *blocks, int n_blocks,
+                       SvtGpuPlan **plan);
+void svtgpu_plan_destroy(SvtGpuPlan *plan);
+
+/* Asynchronous on `cuda_stream` (a cudaStream_t, or NULL for the context's own stream). */
+int svtgpu_run(SvtGpuContext *ctx, const SvtGpuPlan *plan, const SvtGpuBuffers *dev, int stages,
+               void *cuda_stream);
+int svtgpu_sync(SvtGpuContext *ctx);
+/* kernels launched by this context so far */
+long long svtgpu_launch_count(const SvtGpuContext *ctx);
+
+/* thin memory helpers so that a C caller needs no CUDA headers */
+int svtgpu_malloc(SvtGpuContext *ctx, void **dev_ptr, size_t bytes);
+int svtgpu_free(SvtGpuContext *ctx, void *dev_ptr);
+int svtgpu_malloc_host(SvtGpuContext *ctx, void **pinned_ptr, size_t bytes);
+int svtgpu_free_host(SvtGpuContext *ctx, void *pinned_ptr);
+int svtgpu_memcpy_h2d(SvtGpuContext *ctx, void *dev, const void *host, size_t bytes);
+int svtgpu_memcpy_d2h(SvtGpuContext *ctx, void *host, const void *dev, size_t bytes);
+int svtgpu_memset(SvtGpuContext *ctx, void *dev, int value, size_t bytes);
+
+/* scan tables the library generates (av1_scan_orders, EbTransforms.h:3349): for tests */
+int svtgpu_get_iscan(int tx_size, int scan_class, int16_t *iscan_out /* max_eob entries */);
+
+/* ------------------------------------------------------------------------------------------ */
+/* Level B: entry points (host pointers, synchronous)                                          */
+/* ------------------------------------------------------------------------------------------ */
+/* av1_estimate_transform, EbTransforms.h:3896 / EbTransforms.c:4918 */
+int svtgpu_av1_estimate_transform(int16_t *residual_buffer, uint32_t residual_stride,
+                                  int32_t *coeff_buffer, uint32_t coeff_stride,
+                                  uint8_t transform_size, uint64_t *three_quad_energy,
+                                  int16_t *transform_inner_array_ptr, uint32_t bit_increment,
+                                  uint8_t transform_type, int asm_type, int component_type,
+                                  int trans_coeff_shape);
+/* av1_quantize_inv_quantize, EbTransforms.h:3910 / EbFullLoop.c:653, with the table rows that
+ * av1_quantize_inv_quantize_ii selects from the PictureControlSet (:548-613) passed directly */
+void svtgpu_av1_quantize_inv_quantize(const int16_t *zbin, const int16_t *round,
+                                      const int16_t *quant, const int16_t *quant_shift,
+                                      const int16_t *dequant, int32_t *coeff, int32_t *quant_coeff,
+                                      int32_t *recon_coeff, uint8_t txsize, uint16_t *eob,
+                                      uint32_t *y_count_non_zero_coeffs, uint32_t bit_increment,
+                                      uint8_t tx_type, int clamp16);
+/* av1_inv_transform_recon / av1_inv_transform_recon8bit, EbTransforms.h:3967, :3977 */
+int svtgpu_av1_inv_transform_recon(int32_t *coeff_buffer, uint8_t *recon_buffer,
+                                   uint32_t recon_stride, uint8_t txsize, uint32_t bit_increment,
+                                   uint8_t transform_type, int component_type, uint32_t eob);
+int svtgpu_av1_inv_transform_recon8bit(int32_t *coeff_buffer, uint8_t *recon_buffer,
+                                       uint32_t recon_stride, uint8_t txsize,
+                                       uint8_t transform_type, int component_type, uint32_t eob);
+
+/* ------------------------------------------------------------------------------------------ */
+/* Level A: RTCD slots (aom_dsp_rtcd.h)                                                        */
+/* ------------------------------------------------------------------------------------------ */
+#define SVTGPU_FWD_DECL(WxH)                                                                  \
+    void svtgpu_av1_fwd_txfm2d_##WxH(int16_t *input, int32_t *output, uint32_t input_stride, \
+                                     uint8_t transform_type, uint8_t bit_depth);
+/* aom_dsp_rtcd.h:158-255 */
+SVTGPU_FWD_DECL(4x4) SVTGPU_FWD_DECL(8x8) SVTGPU_FWD_DECL(16x16) SVTGPU_FWD_DECL(32x32)
+SVTGPU_FWD_DECL(64x64) SVTGPU_FWD_DECL(4x8) SVTGPU_FWD_DECL(8x4) SVTGPU_FWD_DECL(8x16)
+SVTGPU_FWD_DECL(16x8) SVTGPU_FWD_DECL(16x32) SVTGPU_FWD_DECL(32x16) SVTGPU_FWD_DECL(32x64)
+SVTGPU_FWD_DECL(64x32) SVTGPU_FWD_DECL(4x16) SVTGPU_FWD_DECL(16x4) SVTGPU_FWD_DECL(8x32)
+SVTGPU_FWD_DECL(32x8) SVTGPU_FWD_DECL(16x64) SVTGPU_FWD_DECL(64x16)
+#undef SVTGPU_FWD_DECL
+
+/* aom_dsp_rtcd.h:321-342 (the 8-bit and highbd slots share one prototype) */
+#define SVTGPU_QUANT_DECL(name)                                                                  \
+    void name(const int32_t *coeff_ptr, intptr_t n_coeffs, int32_t skip_block,                  \
+              const int16_t *zbin_ptr, const int16_t *round_ptr, const int16_t *quant_ptr,      \
+              const int16_t *quant_shift_ptr, int32_t *qcoeff_ptr, int32_t *dqcoeff_ptr,        \
+              const int16_t *dequant_ptr, uint16_t *eob_ptr, const int16_t *scan,               \
+              const int16_t *iscan);
+SVTGPU_QUANT_DECL(svtgpu_aom_quantize_b) SVTGPU_QUANT_DECL(svtgpu_aom_quantize_b_32x32)
+SVTGPU_QUANT_DECL(svtgpu_aom_quantize_b_64x64) SVTGPU_QUANT_DECL(svtgpu_aom_highbd_quantize_b)
+SVTGPU_QUANT_DECL(svtgpu_aom_highbd_quantize_b_32x32)
+SVTGPU_QUANT_DECL(svtgpu_aom_highbd_quantize_b_64x64)
+#undef SVTGPU_QUANT_DECL
+
+/* aom_dsp_rtcd.h:347-417: three prototype families */
+#define SVTGPU_INV_SQ_DECL(WxH)                                                          \
+    void svtgpu_av1_inv_txfm2d_add_##WxH(const int32_t *input, uint16_t *output,        \
+                                         int32_t stride, uint8_t tx_type, int32_t bd);
+#define SVTGPU_INV_RECT_DECL(WxH)                                                        \
+    void svtgpu_av1_inv_txfm2d_add_##WxH(const int32_t *input, uint16_t *output,        \
+                                         int32_t stride, uint8_t tx_type, uint8_t tx_size, \
+                                         int32_t eob, int32_t bd);
+#define SVTGPU_INV_4N_DECL(WxH)                                                          \
+    void svtgpu_av1_inv_txfm2d_add_##WxH(const int32_t *input, uint16_t *output,        \
+                                         int32_t stride, uint8_t tx_type, uint8_t tx_size, \
+                                         int32_t bd);
+SVTGPU_INV_SQ_DECL(4x4) SVTGPU_INV_SQ_DECL(8x8) SVTGPU_INV_SQ_DECL(16x16)
+SVTGPU_INV_SQ_DECL(32x32) SVTGPU_INV_SQ_DECL(64x64)
+SVTGPU_INV_RECT_DECL(8x16) SVTGPU_INV_RECT_DECL(16x8) SVTGPU_INV_RECT_DECL(16x32)
+SVTGPU_INV_RECT_DECL(32x16) SVTGPU_INV_RECT_DECL(32x8) SVTGPU_INV_RECT_DECL(8x32)
+SVTGPU_INV_RECT_DECL(32x64) SVTGPU_INV_RECT_DECL(64x32) SVTGPU_INV_RECT_DECL(16x64)
+SVTGPU_INV_RECT_DECL(64x16)
+SVTGPU_INV_4N_DECL(4x8) SVTGPU_INV_4N_DECL(8x4) SVTGPU_INV_4N_DECL(4x16) SVTGPU_INV_4N_DECL(16x4)
+#undef SVTGPU_INV_SQ_DECL
+#undef SVTGPU_INV_RECT_DECL
+#undef SVTGPU_INV_4N_DECL
+
+/* layout-compatible with TxfmParam, EbDefinitions.h:764-776 */
+typedef struct SvtGpuTxfmParam {
+    uint8_t tx_type;
+    uint8_t tx_size;
+    int32_t lossless;
+    int32_t bd;
+    int32_t is_hbd;
+    uint8_t tx_set_type;
+    int32_t eob;
+} SvtGpuTxfmParam;
+/* av1_inv_txfm_add (8-bit pixels), aom_dsp_rtcd.h:421-423 */
+void svtgpu_av1_inv_txfm_add(const int32_t *dqcoeff, uint8_t *dst, int32_t stride,
+                             const SvtGpuTxfmParam *txfm_param);
+
+/* Fills a table of {slot name, function} pairs for the installer shown in INTEGRATION.md. */
+typedef struct SvtGpuRtcdEntry { const char *slot; void *fn; } SvtGpuRtcdEntry;
+int svtgpu_rtcd_table(const SvtGpuRtcdEntry **entries);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SVT_GPU_H */

@@ -557,7 +557,8 @@ int svto_inv_txfm2d_add8(const int32_t *dq, uint8_t *dst, int32_t stride, int s,
 /* the whole path for a slice of a block list (bench.py cpu_baseline "port") */
 void svto_fused_blocks(const SvtoBlock *blk, int first, int last, const int16_t *residual,
                        void *recon, const int16_t *tables, int32_t *qcoeff, int32_t *dqcoeff,
-                       uint16_t *eob, uint64_t *energy, const int16_t *const *scans, int clamp16) {
+                       uint16_t *eob, uint64_t *energy, const int16_t *const *scans, int clamp16,
+                       const uint8_t *wt, const uint8_t *iwt, const int32_t *qm_off) {
     int32_t *coeff = (int32_t *)malloc(sizeof(int32_t) * 4096);
     for (int i = first; i < last; ++i) {
         const SvtoBlock *b = &blk[i];
@@ -566,9 +567,12 @@ void svto_fused_blocks(const SvtoBlock *blk, int first, int last, const int16_t 
         const int16_t *scan = scans[b->tx_size * 3 + svto_scan_class(b->tx_size, b->tx_type)];
         svto_estimate_transform(residual + b->res_off, b->res_stride, coeff, b->tx_size,
                                 b->tx_type, b->bd, &energy[i]);
+        const int use_qm = (b->flags & 2) && wt != NULL;
+        const int qo = use_qm ? qm_off[(b->plane > 0) * 19 + b->tx_size] : 0;
         svto_quantize(coeff, n, t, t + 8, t + 16, t + 24, t + 32, qcoeff + b->coeff_off,
-                      dqcoeff + b->coeff_off, &eob[i], scan, svto_tx_scale(b->tx_size), NULL, NULL,
-                      clamp16 && b->bd == 8);
+                      dqcoeff + b->coeff_off, &eob[i], scan, svto_tx_scale(b->tx_size),
+                      use_qm ? wt + qo : NULL, use_qm ? iwt + qo : NULL,
+                      (clamp16 || (b->flags & 1)) && b->bd == 8);
         if (eob[i]) {
             if (b->bd == 8)
                 svto_inv_txfm2d_add8(dqcoeff + b->coeff_off, (uint8_t *)recon + b->rec_off,

@@ -79,7 +79,8 @@ typedef struct SvtoBlock {
 void svto_fused_blocks(const SvtoBlock *blk, int first, int last, const int16_t *residual,
                        void *recon, const int16_t *tables, int32_t *qcoeff, int32_t *dqcoeff,
                        uint16_t *eob, uint64_t *energy, const int16_t *const *scans,
-                       int clamp16);
+                       int clamp16, const uint8_t *wt, const uint8_t *iwt,
+                       const int32_t *qm_off /* [2][19] or NULL */);
 
 #ifdef __cplusplus
 }

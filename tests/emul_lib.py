@@ -1,0 +1,48 @@
+"""Builds and binds tests/host_emul.cpp: the product's device phase functions compiled for the
+host (test infrastructure; lets the CPU-only tier check kernel arithmetic without a GPU)."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+from oracle_lib import P, ROOT
+
+_lib = None
+
+
+class Buffers(ctypes.Structure):  # SvtGpuBuffers, include/svt_gpu.h
+    _fields_ = [(n, ctypes.c_void_p) for n in ("residual", "pred", "recon", "coeff_in", "coeff",
+                                               "qcoeff", "dqcoeff", "eob", "energy")]
+
+
+def emul():
+    global _lib
+    if _lib is None:
+        src = os.path.join(ROOT, "tests", "host_emul.cpp")
+        out = os.path.join(ROOT, "tests", "_build", "host_emul.so")
+        deps = [src] + [os.path.join(ROOT, "cidana_svt_av1_b200", "csrc", f)
+                        for f in ("txfm1d.cuh", "residual_kernel.cuh", "host_plan.h")]
+        if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(d) for d in deps):
+            os.makedirs(os.path.dirname(out), exist_ok=True)
+            subprocess.check_call(["g++", "-std=c++17", "-O1", "-fwrapv", "-shared", "-fPIC", src,
+                                   "-o", out])
+        _lib = ctypes.CDLL(out)
+    return _lib
+
+
+def run_emul(batch, tables, stages=7, qm=None, coeff_in=None, want_coeff=False):
+    E = emul()
+    n = batch.n_blocks
+    out = dict(qcoeff=np.zeros(batch.n_coeff, np.int32), dqcoeff=np.zeros(batch.n_coeff, np.int32),
+               eob=np.zeros(n, np.uint16), energy=np.zeros(n, np.uint64), recon=batch.pred.copy(),
+               coeff=np.zeros(batch.n_coeff, np.int32) if want_coeff else None)
+    b = Buffers(P(batch.residual), P(batch.pred), P(out["recon"]), P(coeff_in), P(out["coeff"]),
+                P(out["qcoeff"]), P(out["dqcoeff"]), P(out["eob"]), P(out["energy"]))
+    wt = iwt = off = None
+    if qm is not None:
+        wt, iwt, off = qm
+    blocks = np.ascontiguousarray(batch.blocks)
+    rc = E.emul_run_batch(P(blocks), n, ctypes.byref(b), P(tables), P(wt), P(iwt), P(off), stages)
+    assert rc == 0, rc
+    return out

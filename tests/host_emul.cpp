@@ -1,0 +1,71 @@
+// TEST INFRASTRUCTURE ONLY.  Runs the product's device phase functions
+// (cidana_svt_av1_b200/csrc/residual_kernel.cuh) on the host, task by task, so that the kernel
+// arithmetic can be checked against the oracle in the CPU-only test tier.  This is not a CPU
+// fallback: nothing in the product links or loads it.
+#include "../cidana_svt_av1_b200/csrc/host_plan.h"
+#include <vector>
+using namespace svt;
+
+template <int W, int H>
+static void run_size(const KParams& p, int first, int count) {
+    using G = Geo<W, H>;
+    std::vector<int> buf(G::BLK);
+    for (int i = first; i < first + count; ++i) {
+        const DevBlock& d = p.blocks[i];
+        if (p.stages & STAGE_FWD)
+            for (int c = 0; c < W; ++c) phase_fwd_col<W, H>(p, d, c, buf.data());
+        int eob = 0;
+        unsigned long long energy = 0;
+        for (int r = 0; r < H; ++r) {
+            int e; unsigned long long en;
+            phase_row<W, H>(p, d, r, buf.data(), e, en);
+            eob = e > eob ? e : eob;
+            energy += en;
+        }
+        if (p.stages & STAGE_QUANT) p.eob[d.id] = (uint16_t)eob;
+        if ((p.stages & STAGE_FWD) && p.energy) p.energy[d.id] = energy;
+        if (p.stages & STAGE_INV)
+            for (int c = 0; c < W; ++c) phase_inv_col<W, H>(p, d, c, buf.data());
+    }
+}
+
+static int run_bucket(const KParams& p, int tx_size, int first, int count) {
+    switch (tx_size) {
+#define CASE(id, w, h) case id: run_size<w, h>(p, first, count); return 0;
+        CASE(0, 4, 4) CASE(1, 8, 8) CASE(2, 16, 16) CASE(3, 32, 32) CASE(4, 64, 64)
+        CASE(5, 4, 8) CASE(6, 8, 4) CASE(7, 8, 16) CASE(8, 16, 8) CASE(9, 16, 32)
+        CASE(10, 32, 16) CASE(11, 32, 64) CASE(12, 64, 32) CASE(13, 4, 16) CASE(14, 16, 4)
+        CASE(15, 8, 32) CASE(16, 32, 8) CASE(17, 16, 64) CASE(18, 64, 16)
+#undef CASE
+    }
+    return -1;
+}
+
+// Same contract as svtgpu_plan_create + svtgpu_run, with host pointers in `bufs`.
+extern "C" int emul_run_batch(const SvtGpuBlock* blocks, int n, const SvtGpuBuffers* bufs,
+                              const int16_t* qtables, const uint8_t* wt, const uint8_t* iwt,
+                              const int32_t* qm_off, int stages) {
+    std::vector<DevBlock> dev;
+    int first[19], count[19];
+    const int bad = bucket_blocks(blocks, n, dev, first, count);
+    if (bad) return -bad;
+    std::vector<int16_t> iscan;
+    KParams p = {};
+    build_iscan_tables(iscan, p.iscan_off);
+    p.blocks = dev.data(); p.n_blocks = n; p.stages = stages;
+    p.residual = bufs->residual; p.pred = bufs->pred; p.recon = bufs->recon;
+    p.coeff_in = bufs->coeff_in; p.coeff_out = bufs->coeff; p.qcoeff = bufs->qcoeff;
+    p.dqcoeff = bufs->dqcoeff; p.eob = bufs->eob; p.energy = bufs->energy;
+    p.qtables = qtables; p.iscan = iscan.data(); p.qm_wt = wt; p.qm_iwt = iwt;
+    for (int i = 0; i < 2 * 19; ++i) (&p.qm_off[0][0])[i] = qm_off ? qm_off[i] : 0;
+    for (int s = 0; s < 19; ++s)
+        if (count[s]) run_bucket(p, s, first[s], count[s]);
+    return 0;
+}
+extern "C" int emul_get_iscan(int tx_size, int cls, int16_t* out) {
+    std::vector<int16_t> t;
+    make_iscan(tx_size, cls, t);
+    for (size_t i = 0; i < t.size(); ++i) out[i] = t[i];
+    return (int)t.size();
+}
+extern "C" int emul_cospi(int bit, int j) { return kCos.v[bit - 10][j]; }

@@ -102,3 +102,92 @@ def aligned_copy(x, align=64):
     a = aligned(x.shape, x.dtype, align=align)
     a[...] = x
     return a
+
+
+# ---- whole-batch runners (the checker side of the parity tests and of bench.py) -----------------
+def build_tables(qt):
+    """[3*256][5][8] int16: rows plane*256 + qindex, from the golden quantizer tables of one bit
+    depth ({plane: [256][5][8]})."""
+    return np.ascontiguousarray(np.concatenate([qt[0], qt[1], qt[2]], axis=0))
+
+
+def qm_pack(qms, level):
+    """Concatenate the qmatrices of one level into (wt, iwt, off[2][19])."""
+    wt, iwt, off = [], [], np.zeros((2, 19), np.int32)
+    pos = 0
+    for pl in (0, 1):
+        for s in range(19):
+            w, iw = qms[(level, pl, s)]
+            off[pl, s] = pos
+            wt.append(w)
+            iwt.append(iw)
+            pos += len(w)
+    return np.concatenate(wt), np.concatenate(iwt), off
+
+
+def _slices(n, threads):
+    step = (n + threads - 1) // threads
+    return [(i, min(n, i + step)) for i in range(0, n, step)]
+
+
+def run_oracle(batch, tables, scans, clamp16=0, qm=None, threads=1, first=0, last=None):
+    """oracle/svt_oracle.c over batch.blocks[first:last] -> dict of outputs (full-size arrays)."""
+    import threading
+    O = oracle()
+    n = batch.n_blocks
+    last = n if last is None else last
+    q = np.zeros(batch.n_coeff, np.int32)
+    dq = np.zeros(batch.n_coeff, np.int32)
+    eob = np.zeros(n, np.uint16)
+    energy = np.zeros(n, np.uint64)
+    recon = batch.pred.copy()
+    ptrs = (ctypes.c_void_p * (19 * 3))()
+    keep = []
+    for s in range(19):
+        for c in range(3):
+            a = np.ascontiguousarray(scans[(s, c)][0])
+            keep.append(a)
+            ptrs[s * 3 + c] = a.ctypes.data
+    wt = iwt = off = None
+    if qm is not None:
+        wt, iwt, off = qm
+    blocks = np.ascontiguousarray(batch.blocks)
+
+    def work(a, b):
+        O.svto_fused_blocks(P(blocks), a, b, P(batch.residual), P(recon), P(tables), P(q), P(dq),
+                            P(eob), P(energy), ptrs, int(clamp16), P(wt), P(iwt), P(off))
+    sl = [(first + a, first + b) for a, b in _slices(last - first, threads)]
+    if threads == 1:
+        work(*sl[0])
+    else:
+        th = [threading.Thread(target=work, args=x) for x in sl]
+        [t.start() for t in th]
+        [t.join() for t in th]
+    return dict(qcoeff=q, dqcoeff=dq, eob=eob, energy=energy, recon=recon)
+
+
+def run_ref(batch, tables, threads=1, first=0, last=None, asm=1):
+    """The compiled reference (AVX2 RTCD table) over the same arrays; no qmatrix, no clamp16."""
+    import threading
+    R = ref(asm)
+    n = batch.n_blocks
+    last = n if last is None else last
+    q = aligned(batch.n_coeff, np.int32)
+    dq = aligned(batch.n_coeff, np.int32)
+    eob = np.zeros(n, np.uint16)
+    energy = np.zeros(n, np.uint64)
+    recon = aligned_copy(batch.pred)
+    residual = aligned_copy(batch.residual)
+    blocks = np.ascontiguousarray(batch.blocks)
+
+    def work(a, b):
+        R.ref_fused_blocks(P(blocks), a, b, P(residual), P(recon), P(tables), P(q), P(dq), P(eob),
+                           P(energy))
+    sl = [(first + a, first + b) for a, b in _slices(last - first, threads)]
+    if threads == 1:
+        work(*sl[0])
+    else:
+        th = [threading.Thread(target=work, args=x) for x in sl]
+        [t.start() for t in th]
+        [t.join() for t in th]
+    return dict(qcoeff=q, dqcoeff=dq, eob=eob, energy=energy, recon=recon)

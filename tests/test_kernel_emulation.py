@@ -1,0 +1,146 @@
+"""CPU tier: the product's device code (txfm1d.cuh / residual_kernel.cuh / host_plan.h), compiled
+for the host, against the oracle and the golden fixtures.  The GPU tier (test_gpu_parity.py) runs
+the same comparisons through the C ABI on a B200."""
+import ctypes
+
+import numpy as np
+import pytest
+
+from cidana_svt_av1_b200 import workloads as wl
+from emul_lib import emul, run_emul
+from golden_util import load_fused_vectors, load_qmatrices, load_quant_tables, load_scans
+from oracle_lib import P, build_tables, max_eob, oracle, qm_pack, run_oracle
+
+KEYS = ("qcoeff", "dqcoeff", "eob", "energy", "recon")
+
+
+def _tables(bd):
+    qt = load_quant_tables()
+    return build_tables({p: qt[(bd, p)] for p in range(3)})
+
+
+def _check(a, b, what):
+    for k in KEYS:
+        assert np.array_equal(a[k], b[k]), (what, k, np.nonzero(a[k] != b[k])[0][:5])
+
+
+def test_cospi_matches_reference_closed_form():
+    O, E = oracle(), emul()
+    for bit in range(10, 14):
+        ref = np.ctypeslib.as_array(O.svto_cospi(bit), (64,))
+        got = np.array([E.emul_cospi(bit, j) for j in range(64)])
+        assert np.array_equal(ref, got)
+
+
+def test_generated_scans_match_av1_scan_orders():
+    E = emul()
+    scans = load_scans()
+    for s in range(19):
+        for c in range(3):
+            n = max_eob(s)
+            out = np.zeros(n, np.int16)
+            assert E.emul_get_iscan(s, c, P(out)) == n
+            assert np.array_equal(out, scans[(s, c)][1]), (s, c)
+
+
+@pytest.mark.parametrize("bd", [8, 10])
+@pytest.mark.parametrize("strided", [False, True])
+def test_fused_all_pairs(bd, strided):
+    batch = wl.make_packed_batch(wl.valid_pairs(), bd, 3, seed=13596 + bd, strided=strided)
+    tables = _tables(bd)
+    a = run_emul(batch, tables)
+    b = run_oracle(batch, tables, load_scans())
+    _check(a, b, f"bd{bd}")
+    assert (b["eob"] > 0).mean() > 0.5
+
+
+@pytest.mark.parametrize("bd", [8, 10])
+def test_fused_small_residuals_and_zero_blocks(bd):
+    batch = wl.make_packed_batch(wl.valid_pairs(), bd, 2, seed=5, amp_div=64, qindex=(200, 255))
+    batch.residual[: len(batch.residual) // 3] = 0
+    tables = _tables(bd)
+    _check(run_emul(batch, tables), run_oracle(batch, tables, load_scans()), "small")
+
+
+def test_clamp16_variant_8bit():
+    pairs = [(s, 0) for s in range(19)]
+    batch = wl.make_packed_batch(pairs, 8, 3, seed=3, qindex=(0, 1, 2), flags=wl.BLK_CLAMP16)
+    tables = _tables(8)
+    a = run_emul(batch, tables)
+    b = run_oracle(batch, tables, load_scans(), clamp16=1)
+    _check(a, b, "clamp16")
+
+
+def test_qmatrix_10bit():
+    qm = qm_pack(load_qmatrices(), 6)
+    pairs = [(s, t) for s, t in wl.valid_pairs() if t < 9]
+    batch = wl.make_packed_batch(pairs, 10, 2, seed=9, qindex=(100,), flags=wl.BLK_USE_QM)
+    tables = _tables(10)
+    a = run_emul(batch, tables, qm=qm)
+    b = run_oracle(batch, tables, load_scans(), qm=qm)
+    _check(a, b, "qm")
+    flat = run_oracle(batch, tables, load_scans())
+    assert not np.array_equal(flat["qcoeff"], b["qcoeff"])  # the matrices do something
+
+
+def test_stage_split_equals_fused():
+    """fwd-only -> quant-only -> inverse-only (the RTCD-level path) == fused."""
+    batch = wl.make_packed_batch(wl.valid_pairs(), 10, 1, seed=21)
+    tables = _tables(10)
+    fused = run_emul(batch, tables, want_coeff=True)
+    f = run_emul(batch, tables, stages=1, want_coeff=True)
+    assert np.array_equal(f["coeff"], fused["coeff"])
+    q = run_emul(batch, tables, stages=2, coeff_in=f["coeff"])
+    assert np.array_equal(q["qcoeff"], fused["qcoeff"]) and np.array_equal(q["eob"], fused["eob"])
+    i = run_emul(batch, tables, stages=4, coeff_in=q["dqcoeff"])
+    assert np.array_equal(i["recon"], fused["recon"])
+
+
+def test_golden_vectors_from_reference_build():
+    """Known answers produced by the reference's AVX2 path (tests/golden/make_golden.py)."""
+    g = load_fused_vectors()
+    O = oracle()
+    for bd in (8, 10):
+        tables = _tables(bd)
+        pairs = wl.valid_pairs()
+        batch = wl.make_packed_batch(pairs, bd, 1, seed=0)
+        for i, (s, t) in enumerate(pairs):
+            k = f"{bd}_{s}_{t}"
+            o, n = int(batch.blocks["res_off"][i]), wl.TX_W[s] * wl.TX_H[s]
+            batch.residual[o:o + n] = g["res_" + k].ravel()
+            batch.pred[o:o + n] = g["pred_" + k].ravel()
+            batch.blocks["qrow"][i] = int(g["meta_" + k][0])
+        for name, out in (("emul", run_emul(batch, tables, want_coeff=True)),
+                          ("oracle", run_oracle(batch, tables, load_scans()))):
+            for i, (s, t) in enumerate(pairs):
+                k = f"{bd}_{s}_{t}"
+                co, n = int(batch.blocks["coeff_off"][i]), max_eob(s)
+                o, a = int(batch.blocks["res_off"][i]), wl.TX_W[s] * wl.TX_H[s]
+                meta = g["meta_" + k]
+                assert np.array_equal(out["qcoeff"][co:co + n], g["q_" + k]), (name, k)
+                assert np.array_equal(out["dqcoeff"][co:co + n], g["dq_" + k]), (name, k)
+                assert out["eob"][i] == meta[1], (name, k)
+                assert int(out["energy"][i]) == int(meta[2]) + (int(meta[3]) << 32), (name, k)
+                assert np.array_equal(out["recon"][o:o + a], g["rec_" + k].ravel()), (name, k)
+                if name == "emul":
+                    assert np.array_equal(out["coeff"][co:co + n], g["coeff_" + k]), (name, k)
+
+
+def test_frame_batch_small():
+    batch = wl.make_frame_batch(256, 128, 1, 8, seed=20240)
+    tables = _tables(8)
+    _check(run_emul(batch, tables), run_oracle(batch, tables, load_scans()), "frame8")
+    batch = wl.make_frame_batch(192, 128, 1, 10, seed=20241, qindex=100, laplace_b=24.0)
+    tables = _tables(10)
+    _check(run_emul(batch, tables), run_oracle(batch, tables, load_scans()), "frame10")
+
+
+def test_plan_rejects_bad_blocks():
+    E = emul()
+    batch = wl.make_packed_batch([(4, 0)], 8, 1, seed=1)
+    tables = _tables(8)
+    for field, val in (("tx_type", 1), ("bd", 12), ("coeff_off", 2), ("tx_size", 19)):
+        bad = wl.make_packed_batch([(4, 0)], 8, 1, seed=1)
+        bad.blocks[field] = val
+        with pytest.raises(AssertionError):
+            run_emul(bad, tables)
