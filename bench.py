@@ -1,0 +1,325 @@
+#!/usr/bin/env python
+"""bench.py -- fused fwd-txfm + quant + inv-recon throughput (Mcoeff/s) and HBM roofline.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload 1080p8|4k10qm|4k10]
+    python bench.py --impl reference ...     # the reference's CPU path on the host cores
+
+One "step" = one pass of the hot path over one synthetic frame batch.  `value` is
+device-resident throughput (CUDA events on the launching stream, max over ranks); `e2e` is the
+same metric through the host-buffer call (H2D of residual/prediction/descriptors and D2H of every
+output inside the timed region).  Multi-GPU: one process per GPU, frames sharded (each rank owns
+its own frame batch: weak scaling), no collective on the data path.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+from cidana_svt_av1_b200 import workloads as wl  # noqa: E402
+
+METRIC = "fwd-txfm+quant+inv-recon throughput"
+UNIT = "Mcoeff/s"
+
+WORKLOADS = {
+    # name: (maker kwargs, description)
+    "1080p8": (dict(width=1920, height=1080, n_frames=16, bd=8, seed=20240, qindex=120,
+                    laplace_b=6.0), "1080p 8-bit frame batch, 16 frames, mixed TX sizes"),
+    "4k10qm": (dict(width=3840, height=2160, n_frames=4, bd=10, seed=20241, qindex=100,
+                    laplace_b=24.0, use_qm=True), "4K 10-bit frame batch with qmatrix, 4 frames"),
+    "4k10": (dict(width=3840, height=2160, n_frames=4, bd=10, seed=20241, qindex=100,
+                  laplace_b=24.0), "4K 10-bit frame batch, 4 frames"),
+    "tiny": (dict(width=256, height=128, n_frames=1, bd=8, seed=1), "smoke-size batch"),
+}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+def make_batch(name, rank):
+    kw = dict(WORKLOADS[name][0])
+    kw["seed"] = kw["seed"] + 1000 * rank
+    return wl.make_frame_batch(**kw)
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+        self.proc = None
+
+    def run(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.index), "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            for line in self.proc.stdout:
+                self.rows.append([x.strip() for x in line.split(",")])
+                if self.stop_flag:
+                    break
+        except Exception:
+            pass
+
+    def finish(self):
+        self.stop_flag = True
+        if self.proc:
+            self.proc.terminate()
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i] == "Active"})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def load_tables(bd):
+    from golden_util import build_tables, load_quant_tables
+    qt = load_quant_tables()
+    return build_tables({p: qt[(bd, p)] for p in range(3)})
+
+
+def load_qm():
+    from golden_util import load_qmatrices, qm_pack
+    return qm_pack(load_qmatrices(), 6)  # aom_get_qmlevel(100, 5, 9)
+
+
+# ---- the reference arm / cpu_baseline --------------------------------------------------------------
+def make_cpu_runner(batch, tables, qm):
+    from golden_util import load_scans
+    from oracle_lib import CpuRunner
+    return CpuRunner(batch, tables, scans=load_scans(), qm=qm)
+
+
+def cpu_baseline(batch, tables, qm, budget_s=12.0):
+    """The reference compiled from source (oracle/_ref, kind 'reference') when present and
+    applicable, else the oracle port, on all host cores; best pass within a bounded time."""
+    cores = os.cpu_count() or 1
+    runner = make_cpu_runner(batch, tables, qm)
+    best, passes, t_start = None, 0, time.perf_counter()
+    while passes < 2 or (time.perf_counter() - t_start < budget_s and passes < 200):
+        dt = runner.run(cores)
+        best = dt if best is None else min(best, dt)
+        passes += 1
+    return {"value": batch.n_samples / best / 1e6, "unit": UNIT, "cores": cores, "kind": runner.kind,
+            "sample": f"{passes} passes over the full {batch.name} batch ({batch.n_samples} samples), "
+                      f"best pass, {cores} threads"}
+
+
+def reference_arm(args, rank, world):
+    """--impl reference: the reference's own CPU implementation of the path (oracle/_ref when it was
+    compiled, else the oracle port) on all host threads; each step = one pass over the workload."""
+    if rank != 0:
+        return 0
+    batch = make_batch(args.workload, 0)
+    tables = load_tables(batch.bd)
+    qm = load_qm() if "qm" in args.workload else None
+    cores = os.cpu_count() or 1
+    runner = make_cpu_runner(batch, tables, qm)
+    for _ in range(args.warmup):
+        runner.run(cores)
+    t = sum(runner.run(cores) for _ in range(args.steps))
+    val = batch.n_samples * args.steps / t / 1e6
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32",
+            "data": "synthetic", "config": {"workload": WORKLOADS[args.workload][1], "name": batch.name,
+                                            "samples_per_step": batch.n_samples, "blocks": batch.n_blocks},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": runner.kind,
+                             "sample": f"each step = one pass over the full batch, {cores} threads"},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def gpu_arm(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    import cidana_svt_av1_b200 as pkg
+
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    batch = make_batch(args.workload, rank)
+    tables = load_tables(batch.bd)
+    qm = load_qm() if "qm" in args.workload else None
+    g = pkg.SvtGpu(local_rank)
+    g.upload_quant_tables(tables)
+    if qm is not None:
+        g.upload_qmatrix(*qm)
+    plan = g.plan(batch.blocks)
+    st = torch.cuda.Stream(dev)
+    pdt = np.uint8 if batch.bd == 8 else np.int16
+    with torch.cuda.stream(st):
+        h_res = torch.from_numpy(batch.residual).pin_memory()
+        h_pred = torch.from_numpy(batch.pred.view(pdt)).pin_memory()
+        d = dict(residual=h_res.to(dev), pred=h_pred.to(dev))
+        d["recon"] = torch.empty_like(d["pred"])
+        d["qcoeff"] = torch.empty(batch.n_coeff, dtype=torch.int32, device=dev)
+        d["dqcoeff"] = torch.empty(batch.n_coeff, dtype=torch.int32, device=dev)
+        d["eob"] = torch.empty(batch.n_blocks, dtype=torch.int16, device=dev)
+        d["energy"] = torch.empty(batch.n_blocks, dtype=torch.int64, device=dev)
+    st.synchronize()
+
+    def step():
+        g.run(plan, pkg.api.STAGE_ALL, st.cuda_stream, **d)
+
+    def barrier():
+        st.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+        time.sleep(0.3)
+    l0 = g.launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record(st)
+    for _ in range(args.steps):
+        step()
+    e1.record(st)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = g.launches - l0
+    if sampler:
+        # keep the GPU busy a little longer so the 100 ms sampler sees clocks under load
+        t_end = time.time() + 1.0
+        while time.time() < t_end:
+            step()
+        st.synchronize()
+    clocks = sampler.finish() if sampler else None
+    t_ms = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
+    ms = float(t_ms.item())
+    samples = torch.tensor([batch.n_samples], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(samples, op=dist.ReduceOp.SUM)
+    total_samples = float(samples.item())
+    value = total_samples * args.steps / (ms * 1e-3) / 1e6
+
+    # ---- roofline of the dominant kernel, timed alone on the launching stream --------------------
+    hbm, which = peaks()
+    sizes = batch.blocks["tx_size"]
+    by_size = {int(s): int((wl.AREA[sizes[sizes == s]]).sum()) for s in np.unique(sizes)}
+    dom = max(by_size, key=by_size.get)
+    sub_blocks = batch.blocks[sizes == dom]
+    sub = wl.Batch(sub_blocks, batch.residual, batch.pred, batch.n_coeff, batch.bd, "dominant")
+    plan_dom = g.plan(sub_blocks)
+    for _ in range(3):
+        g.run(plan_dom, pkg.api.STAGE_ALL, st.cuda_stream, **d)
+    reps = 20
+    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    st.synchronize()
+    k0.record(st)
+    for _ in range(reps):
+        g.run(plan_dom, pkg.api.STAGE_ALL, st.cuda_stream, **d)
+    k1.record(st)
+    st.synchronize()
+    k_ms = k0.elapsed_time(k1) / reps
+    k_bytes = sub.algorithmic_bytes()
+    achieved = k_bytes / (k_ms * 1e-3) / 1e9
+    roof = {"bound": "hbm", "kernel": f"residual_kernel<{wl.TX_W[dom]},{wl.TX_H[dom]}>",
+            "achieved": achieved, "peak": hbm, "peak_source": which, "unit": "GB/s", "frac": achieved / hbm,
+            "traffic": None, "launch_ms": k_ms, "algorithmic_bytes_per_launch": k_bytes,
+            "step_achieved": batch.algorithmic_bytes() / (ms / args.steps * 1e-3) / 1e9,
+            "step_frac": batch.algorithmic_bytes() / (ms / args.steps * 1e-3) / 1e9 / hbm}
+    tf = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tf):
+        try:
+            roof["traffic"] = json.load(open(tf)).get(f"{args.workload}:{roof['kernel']}")
+        except Exception:
+            pass
+
+    # ---- e2e: host buffers in, host buffers out, copies and descriptor upload in the timed region -
+    with torch.cuda.stream(st):
+        h_out = {k: torch.empty(v.shape, dtype=v.dtype).pin_memory() for k, v in d.items()
+                 if k in ("recon", "qcoeff", "dqcoeff", "eob", "energy")}
+    h2d = h_res.numel() * 2 + h_pred.numel() * h_pred.element_size() + batch.n_blocks * 32
+    d2h = sum(v.numel() * v.element_size() for v in h_out.values())
+
+    def e2e_step():
+        p = g.plan(batch.blocks)  # validate + bucket + upload the descriptors
+        with torch.cuda.stream(st):
+            d["residual"].copy_(h_res, non_blocking=True)
+            d["pred"].copy_(h_pred, non_blocking=True)
+            g.run(p, pkg.api.STAGE_ALL, st.cuda_stream, **d)
+            for k, v in h_out.items():
+                v.copy_(d[k], non_blocking=True)
+        st.synchronize()
+        p.close()
+
+    e2e_steps = max(2, min(args.steps, 5))
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    barrier()
+    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_val = total_samples * e2e_steps / float(e2e_s.item()) / 1e6
+
+    if rank == 0:
+        cpu = None
+        if world == 1 and not args.no_cpu:
+            cpu = cpu_baseline(batch, tables, qm)
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+                "config": {"workload": WORKLOADS[args.workload][1], "name": batch.name,
+                           "samples_per_step_per_gpu": batch.n_samples, "blocks_per_gpu": batch.n_blocks,
+                           "bytes_per_step_per_gpu": batch.algorithmic_bytes(),
+                           "l2": "inputs+outputs per step (>= 550 MB) exceed the 126 MB L2; no flush needed",
+                           "parallelism": f"frames sharded over {world} GPU(s), no collective"},
+                "roofline": roof, "cpu_baseline": cpu, "clocks": clocks, "gpu_launches": launches,
+                "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+                        "d2h_bytes_per_step": int(d2h), "steps": e2e_steps}}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="1080p8", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        return reference_arm(args, rank, world)
+    return gpu_arm(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,240 @@
+"""Host-side mirror of the reference interface over libsvtgpu.so (ctypes; see include/svt_gpu.h).
+
+Level C (batch): ``SvtGpu`` -- context, table upload, plans, device-resident runs on torch CUDA
+tensors, and ``run_host`` (host numpy in / host numpy out, copies included: the e2e call).
+Level B: ``av1_estimate_transform``, ``av1_quantize_inv_quantize``, ``av1_inv_transform_recon``,
+``av1_inv_transform_recon8bit`` -- same names and argument meaning as the reference's
+Source/Lib/Common/Codec/EbTransforms.h:3896-3987, numpy host arrays, synchronous.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+from .workloads import BLOCK_DTYPE, TX_H, TX_W, coded_count
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libsvtgpu.so")
+
+STAGE_FWD, STAGE_QUANT, STAGE_INV, STAGE_ALL = 1, 2, 4, 7
+
+
+class SvtGpuError(RuntimeError):
+    pass
+
+
+class _Buffers(ctypes.Structure):  # SvtGpuBuffers
+    _fields_ = [(n, ctypes.c_void_p) for n in ("residual", "pred", "recon", "coeff_in", "coeff",
+                                               "qcoeff", "dqcoeff", "eob", "energy")]
+
+
+_lib = None
+
+
+def load_library():
+    """Loads libsvtgpu.so.  Raises if it was never built: there is no fallback path."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise SvtGpuError(f"{LIB_PATH} is missing: run `python -m cidana_svt_av1_b200.build` "
+                              "(or __graft_entry__.build()); this package has no CPU fallback")
+        L = ctypes.CDLL(LIB_PATH)
+        L.svtgpu_last_error.restype = ctypes.c_char_p
+        L.svtgpu_launch_count.restype = ctypes.c_longlong
+        L.svtgpu_launch_count.argtypes = [ctypes.c_void_p]
+        L.svtgpu_run.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
+                                 ctypes.c_void_p]
+        L.svtgpu_plan_create.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
+                                         ctypes.c_void_p]
+        L.svtgpu_plan_destroy.argtypes = [ctypes.c_void_p]
+        L.svtgpu_destroy.argtypes = [ctypes.c_void_p]
+        L.svtgpu_sync.argtypes = [ctypes.c_void_p]
+        L.svtgpu_upload_quant_tables.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
+        L.svtgpu_upload_qmatrix.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                            ctypes.c_int, ctypes.c_void_p]
+        _lib = L
+    return _lib
+
+
+def lib():
+    return load_library()
+
+
+def _P(a):
+    return a.ctypes.data_as(ctypes.c_void_p) if a is not None else None
+
+
+def _check(rc, what):
+    if rc != 0:
+        raise SvtGpuError(f"{what} failed ({rc}): {lib().svtgpu_last_error().decode()}")
+
+
+class Plan:
+    def __init__(self, owner, handle, n_blocks):
+        self.owner, self.handle, self.n_blocks = owner, handle, n_blocks
+
+    def close(self):
+        if self.handle:
+            lib().svtgpu_plan_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class SvtGpu:
+    """One context per GPU (one process per GPU in multi-GPU runs)."""
+
+    def __init__(self, device=0):
+        L = load_library()
+        h = ctypes.c_void_p()
+        _check(L.svtgpu_create(ctypes.byref(h), int(device)), "svtgpu_create")
+        self.handle = h
+        self.device = int(device)
+
+    def close(self):
+        if self.handle:
+            lib().svtgpu_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def launches(self):
+        return int(lib().svtgpu_launch_count(self.handle))
+
+    def upload_quant_tables(self, tables):
+        t = np.ascontiguousarray(tables, np.int16).reshape(-1, 5, 8)
+        _check(lib().svtgpu_upload_quant_tables(self.handle, _P(t), t.shape[0]), "upload_quant_tables")
+
+    def upload_qmatrix(self, wt, iwt, off):
+        wt = np.ascontiguousarray(wt, np.uint8)
+        iwt = np.ascontiguousarray(iwt, np.uint8)
+        off = np.ascontiguousarray(off, np.int32).reshape(2, 19)
+        _check(lib().svtgpu_upload_qmatrix(self.handle, _P(wt), _P(iwt), wt.size, _P(off)),
+               "upload_qmatrix")
+
+    def plan(self, blocks):
+        b = np.ascontiguousarray(blocks, BLOCK_DTYPE)
+        h = ctypes.c_void_p()
+        _check(lib().svtgpu_plan_create(self.handle, _P(b), len(b), ctypes.byref(h)), "plan_create")
+        return Plan(self, h, len(b))
+
+    def run(self, plan, stages=STAGE_ALL, stream=None, **bufs):
+        """bufs: torch CUDA tensors (or raw device addresses) named as in SvtGpuBuffers."""
+        def ptr(x):
+            if x is None:
+                return None
+            return int(x) if isinstance(x, int) else x.data_ptr()
+        b = _Buffers(*[ptr(bufs.get(n)) for n, _ in _Buffers._fields_])
+        _check(lib().svtgpu_run(self.handle, plan.handle, ctypes.byref(b), int(stages), stream),
+               "svtgpu_run")
+
+    def sync(self):
+        _check(lib().svtgpu_sync(self.handle), "svtgpu_sync")
+
+    # ---- the end-to-end call: host buffers in, host buffers out -----------------------------------
+    def run_host(self, batch, stages=STAGE_ALL, want_coeff=False, coeff_in=None, plan=None):
+        """Uploads the batch (residual, prediction, block list), runs, downloads every output.
+        Returns a dict of numpy arrays like the oracle runners do."""
+        import torch
+        dev = torch.device("cuda", self.device)
+        own_plan = plan is None
+        if own_plan:
+            plan = self.plan(batch.blocks)
+        # a real (non-legacy) stream: handle 0 would mean "the context's own stream" to the library
+        if getattr(self, "_stream", None) is None:
+            self._stream = torch.cuda.Stream(dev)
+        st = self._stream
+        with torch.cuda.device(dev), torch.cuda.stream(st):
+            res = torch.from_numpy(batch.residual).to(dev, non_blocking=True)
+            pred = torch.from_numpy(batch.pred.view(np.uint8 if batch.bd == 8 else np.int16)).to(dev, non_blocking=True)
+            recon = pred.clone()
+            n = batch.n_blocks
+            q = torch.zeros(batch.n_coeff, dtype=torch.int32, device=dev)
+            dq = torch.zeros(batch.n_coeff, dtype=torch.int32, device=dev)
+            cf = torch.zeros(batch.n_coeff, dtype=torch.int32, device=dev) if want_coeff else None
+            cin = torch.from_numpy(coeff_in).to(dev) if coeff_in is not None else None
+            eob = torch.zeros(n, dtype=torch.int16, device=dev)
+            energy = torch.zeros(n, dtype=torch.int64, device=dev)
+            self.run(plan, stages, st.cuda_stream, residual=res, pred=pred, recon=recon, coeff_in=cin,
+                     coeff=cf, qcoeff=q, dqcoeff=dq, eob=eob, energy=energy)
+            out = dict(qcoeff=q.cpu().numpy(), dqcoeff=dq.cpu().numpy(),
+                       eob=eob.cpu().numpy().view(np.uint16), energy=energy.cpu().numpy().view(np.uint64),
+                       recon=recon.cpu().numpy().view(batch.pred.dtype),
+                       coeff=cf.cpu().numpy() if want_coeff else None)
+        st.synchronize()
+        if own_plan:
+            plan.close()
+        return out
+
+
+# ---- Level B mirrors: the reference's entry points on host numpy arrays ----------------------------
+def av1_estimate_transform(residual_buffer, residual_stride, transform_size, transform_type,
+                           bit_increment=0):
+    """av1_estimate_transform (EbTransforms.c:4918).  residual_buffer: int16 array holding the
+    block at `residual_stride`.  Returns (coeff int32[max_eob], three_quad_energy)."""
+    L = lib()
+    res = np.ascontiguousarray(residual_buffer, np.int16)
+    coeff = np.zeros(TX_W[transform_size] * TX_H[transform_size], np.int32)
+    energy = ctypes.c_uint64(0)
+    rc = L.svtgpu_av1_estimate_transform(_P(res), ctypes.c_uint32(residual_stride), _P(coeff),
+                                         ctypes.c_uint32(0), ctypes.c_uint8(transform_size),
+                                         ctypes.byref(energy), None, ctypes.c_uint32(bit_increment),
+                                         ctypes.c_uint8(transform_type), 0, 0, 0)
+    _check(rc, "av1_estimate_transform")
+    return coeff[:coded_count(transform_size)].copy(), int(energy.value)
+
+
+def av1_quantize_inv_quantize(coeff, table_row, txsize, tx_type, bit_increment=0, clamp16=False):
+    """av1_quantize_inv_quantize (EbFullLoop.c:653) with the quantizer table row
+    (int16[5][8]: zbin, round, quant, quant_shift, dequant) that the reference would pick from the
+    PictureControlSet.  Returns (quant_coeff, recon_coeff, eob)."""
+    L = lib()
+    cf = np.ascontiguousarray(coeff, np.int32)
+    tb = np.ascontiguousarray(table_row, np.int16).reshape(5, 8)
+    n = coded_count(txsize)
+    q = np.zeros(n, np.int32)
+    dq = np.zeros(n, np.int32)
+    eob = ctypes.c_uint16(0)
+    cnt = ctypes.c_uint32(0)
+    L.svtgpu_av1_quantize_inv_quantize(_P(tb[0]), _P(tb[1]), _P(tb[2]), _P(tb[3]), _P(tb[4]), _P(cf),
+                                       _P(q), _P(dq), ctypes.c_uint8(txsize), ctypes.byref(eob),
+                                       ctypes.byref(cnt), ctypes.c_uint32(bit_increment),
+                                       ctypes.c_uint8(tx_type), int(bool(clamp16)))
+    return q, dq, int(eob.value)
+
+
+def av1_inv_transform_recon8bit(coeff_buffer, recon_buffer, recon_stride, txsize, transform_type,
+                                eob=0):
+    """av1_inv_transform_recon8bit (EbTransforms.c:8935): recon_buffer (uint8, prediction in) is
+    updated in place."""
+    L = lib()
+    cf = np.ascontiguousarray(coeff_buffer, np.int32)
+    assert recon_buffer.dtype == np.uint8 and recon_buffer.flags.c_contiguous
+    _check(L.svtgpu_av1_inv_transform_recon8bit(_P(cf), _P(recon_buffer), ctypes.c_uint32(recon_stride),
+                                                ctypes.c_uint8(txsize), ctypes.c_uint8(transform_type),
+                                                0, ctypes.c_uint32(eob)), "av1_inv_transform_recon8bit")
+    return recon_buffer
+
+
+def av1_inv_transform_recon(coeff_buffer, recon_buffer, recon_stride, txsize, bit_increment,
+                            transform_type, eob=0):
+    """av1_inv_transform_recon (EbTransforms.c:8905): 16-bit pixels; the C symbol takes the
+    reference's CONVERT_TO_BYTEPTR form of the pointer, which this wrapper produces."""
+    L = lib()
+    cf = np.ascontiguousarray(coeff_buffer, np.int32)
+    assert recon_buffer.dtype == np.uint16 and recon_buffer.flags.c_contiguous
+    byteptr = ctypes.c_void_p(recon_buffer.ctypes.data >> 1)
+    _check(L.svtgpu_av1_inv_transform_recon(_P(cf), byteptr, ctypes.c_uint32(recon_stride),
+                                            ctypes.c_uint8(txsize), ctypes.c_uint32(bit_increment),
+                                            ctypes.c_uint8(transform_type), 0, ctypes.c_uint32(eob)),
+           "av1_inv_transform_recon")
+    return recon_buffer

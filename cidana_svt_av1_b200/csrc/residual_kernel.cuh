@@ -27,7 +27,10 @@ static inline int4 make_int4(int x, int y, int z, int w) { return int4{ x, y, z,
 
 namespace svt {
 
-enum : int { STAGE_FWD = 1, STAGE_QUANT = 2, STAGE_INV = 4, STAGE_ALL = 7 };
+enum : int { STAGE_FWD = 1, STAGE_QUANT = 2, STAGE_INV = 4, STAGE_ALL = 7,
+             // internal: write all W x H coefficients at stride W (what the RTCD-level
+             // av1_fwd_txfm2d_WxH returns before av1_estimate_transform packs 64-point sizes)
+             STAGE_FWD_FULL = 8 };
 enum : uint32_t { META_TYPE_MASK = 0xF, META_BD10 = 1u << 4, META_PLANE_SHIFT = 5,
                   META_CLAMP16 = 1u << 8, META_USE_QM = 1u << 9 };
 
@@ -167,55 +170,49 @@ SVT_HD void phase_fwd_col(const KParams& p, const DevBlock& d, int c, int* buf /
 }
 
 // ---- quantizer for one coefficient ---------------------------------------------------------------
-struct QRow {  // {DC, AC} pairs with zbin / round already scaled by log_scale
-    int zbin[2], round[2], quant[2], qshift[2], dequant[2];
-};
+struct QSet { int zbin, round, quant, qshift, dequant; };  // one of {DC, AC}
+struct QRow { QSet dc, ac; };  // zbin / round already scaled by log_scale
 template <int LOG_SCALE>
 SVT_HD QRow load_qrow(const int16_t* t) {
+    constexpr int rnd = LOG_SCALE ? (1 << (LOG_SCALE - 1)) : 0;
     QRow q;
-#pragma unroll
-    for (int i = 0; i < 2; ++i) {
-        constexpr int rnd = LOG_SCALE ? (1 << (LOG_SCALE - 1)) : 0;
-        q.zbin[i] = (int(t[i]) + rnd) >> LOG_SCALE;       // ROUND_POWER_OF_TWO, EbFullLoop.c:246
-        q.round[i] = (int(t[8 + i]) + rnd) >> LOG_SCALE;  // EbFullLoop.c:280
-        q.quant[i] = t[16 + i];
-        q.qshift[i] = t[24 + i];
-        q.dequant[i] = t[32 + i];
-    }
+    // ROUND_POWER_OF_TWO(zbin / round, log_scale), EbFullLoop.c:246, :280
+    q.dc = QSet{ (int(t[0]) + rnd) >> LOG_SCALE, (int(t[8]) + rnd) >> LOG_SCALE, t[16], t[24], t[32] };
+    q.ac = QSet{ (int(t[1]) + rnd) >> LOG_SCALE, (int(t[9]) + rnd) >> LOG_SCALE, t[17], t[25], t[33] };
     return q;
 }
 // flat (no qmatrix): aom_highbd_quantize_b*_avx2 arithmetic
 // (Source/Lib/Common/ASM_AVX2/highbd_quantize_intrin_avx2.c:80-125), equal to
 // highbd_quantize_b_helper_c (EbFullLoop.c:239) for the tables av1_build_quantizer produces.
 template <int LOG_SCALE>
-SVT_HD void quant_flat(int cf, const QRow& q, int ac, bool clamp16, int& qc, int& dqc) {
+SVT_HD void quant_flat(int cf, const QSet& q, bool clamp16, int& qc, int& dqc) {
     const int sign = cf >> 31;
     const int ab = (cf ^ sign) - sign;
     qc = 0; dqc = 0;
-    if (ab >= q.zbin[ac]) {
-        int t1 = ab + q.round[ac];
+    if (ab >= q.zbin) {
+        int t1 = ab + q.round;
         if (clamp16) t1 = t1 > 32767 ? 32767 : t1;  // 8-bit C variant, EbFullLoop.c:86-88
-        const int64_t p1 = int64_t(t1) * q.quant[ac];
+        const int64_t p1 = int64_t(t1) * q.quant;
         const uint32_t t2 = uint32_t(uint64_t(p1) >> 16) + uint32_t(t1);
-        const uint64_t p2 = uint64_t(t2) * uint32_t(q.qshift[ac]);
+        const uint64_t p2 = uint64_t(t2) * uint32_t(q.qshift);
         const int aq = int(uint32_t(p2 >> (16 - LOG_SCALE)));
-        const int adq = int(unsigned(aq) * unsigned(q.dequant[ac])) >> LOG_SCALE;
+        const int adq = int(unsigned(aq) * unsigned(q.dequant)) >> LOG_SCALE;
         qc = (aq ^ sign) - sign;
         dqc = (adq ^ sign) - sign;
     }
 }
 // with quantization matrices: highbd_quantize_b_helper_c, EbFullLoop.c:239-296
 template <int LOG_SCALE>
-SVT_HD void quant_qm(int cf, const QRow& q, int ac, int wt, int iwt, int& qc, int& dqc) {
+SVT_HD void quant_qm(int cf, const QSet& q, int wt, int iwt, int& qc, int& dqc) {
     const int sign = cf >> 31;
     const int ab = (cf ^ sign) - sign;
     const int cw = int(unsigned(cf) * unsigned(wt));
     qc = 0; dqc = 0;
-    if (cw >= q.zbin[ac] * 32 || cw <= -q.zbin[ac] * 32) {
-        const int64_t tw = (int64_t(ab) + q.round[ac]) * wt;
-        const int64_t t2 = ((tw * q.quant[ac]) >> 16) + tw;
-        const int aq = int((t2 * q.qshift[ac]) >> (16 - LOG_SCALE + 5));
-        const int dq = (q.dequant[ac] * iwt + 16) >> 5;
+    if (cw >= q.zbin * 32 || cw <= -q.zbin * 32) {
+        const int64_t tw = (int64_t(ab) + q.round) * wt;
+        const int64_t t2 = ((tw * q.quant) >> 16) + tw;
+        const int aq = int((t2 * q.qshift) >> (16 - LOG_SCALE + 5));
+        const int dq = (q.dequant * iwt + 16) >> 5;
         const int adq = int(unsigned(aq) * unsigned(dq)) >> LOG_SCALE;
         qc = (aq ^ sign) - sign;
         dqc = (adq ^ sign) - sign;
@@ -254,7 +251,12 @@ SVT_HD void phase_row(const KParams& p, const DevBlock& d, int r, int* buf, int&
                 if (r >= KH || c >= KW)
                     energy_sum += (unsigned long long)(int64_t(x[c]) * int64_t(x[c]));
         }
-        if (p.coeff_out && r < KH) {
+        if (p.stages & STAGE_FWD_FULL) {
+#pragma unroll
+            for (int c = 0; c < W; c += 4)
+                *reinterpret_cast<int4*>(p.coeff_out + d.coeff_off + r * W + c) =
+                    make_int4(x[c], x[c + 1], x[c + 2], x[c + 3]);
+        } else if (p.coeff_out && r < KH) {
 #pragma unroll
             for (int c = 0; c < KW; c += 4)
                 *reinterpret_cast<int4*>(p.coeff_out + cbase + c) =
@@ -270,6 +272,7 @@ SVT_HD void phase_row(const KParams& p, const DevBlock& d, int r, int* buf, int&
 
     if ((p.stages & STAGE_QUANT) && r < KH) {
         const QRow q = load_qrow<LS>(p.qtables + size_t(d.qrow) * 40);
+        const QSet q0 = r == 0 ? q.dc : q.ac;
         const int cls = t < 10 ? 0 : ((t & 1) ? 2 : 1);  // av1_scan_orders, EbTransforms.h:3349
         const int16_t* iscan = p.iscan + p.iscan_off[G::TXS][cls] + r * KW;
         const bool clamp16 = d.meta & META_CLAMP16;
@@ -283,9 +286,9 @@ SVT_HD void phase_row(const KParams& p, const DevBlock& d, int r, int* buf, int&
             for (int j = 0; j < 4; ++j) {
                 const int c = c0 + j;
                 int dqc;
-                const int ac = (r | c) != 0;
-                if (!use_qm) quant_flat<LS>(x[c], q, ac, clamp16, qv[j], dqc);
-                else quant_qm<LS>(x[c], q, ac, p.qm_wt[qmo + c], p.qm_iwt[qmo + c], qv[j], dqc);
+                const QSet& qs = (c == 0) ? q0 : q.ac;  // position 0 of the block is DC
+                if (!use_qm) quant_flat<LS>(x[c], qs, clamp16, qv[j], dqc);
+                else quant_qm<LS>(x[c], qs, p.qm_wt[qmo + c], p.qm_iwt[qmo + c], qv[j], dqc);
                 x[c] = dqc;
                 if (qv[j] != 0) { const int s = int(iscan[c]) + 1; e = s > e ? s : e; }
             }
@@ -399,6 +402,32 @@ residual_kernel(const __grid_constant__ KParams p, int first_block, int count) {
             if (b < nb) phase_inv_col<W, H>(p, sh.blk[b], c, buf + b * G::BLK);
         }
     }
+}
+
+// Stand-alone quantizer behind the RTCD slots aom_[highbd_]quantize_b[_32x32|_64x64]
+// (aom_dsp_rtcd.h:321-342): the caller supplies n_coeffs and its own iscan, not a tx_size.
+// One CTA per call; eob = max(iscan + 1) over non-zero levels.
+template <int LOG_SCALE>
+__global__ void __launch_bounds__(256)
+quant_kernel(const int32_t* coeff, int n, const int16_t* tab /* 5 x {DC, AC} */,
+             const int16_t* iscan, int32_t* qcoeff, int32_t* dqcoeff, uint16_t* eob) {
+    constexpr int rnd = LOG_SCALE ? (1 << (LOG_SCALE - 1)) : 0;
+    const QSet dc{ (int(tab[0]) + rnd) >> LOG_SCALE, (int(tab[2]) + rnd) >> LOG_SCALE, tab[4], tab[6], tab[8] };
+    const QSet ac{ (int(tab[1]) + rnd) >> LOG_SCALE, (int(tab[3]) + rnd) >> LOG_SCALE, tab[5], tab[7], tab[9] };
+    __shared__ int s_eob;
+    if (threadIdx.x == 0) s_eob = 0;
+    __syncthreads();
+    int e = 0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        int qc, dqc;
+        quant_flat<LOG_SCALE>(coeff[i], i == 0 ? dc : ac, false, qc, dqc);
+        qcoeff[i] = qc;
+        dqcoeff[i] = dqc;
+        if (qc != 0) { const int s = int(iscan[i]) + 1; e = s > e ? s : e; }
+    }
+    if (e) atomicMax(&s_eob, e);
+    __syncthreads();
+    if (threadIdx.x == 0) *eob = uint16_t(s_eob);
 }
 #endif
 

@@ -1,0 +1,48 @@
+// Internal definitions shared by the translation units of libsvtgpu.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/svt_gpu.h"
+#include "residual_kernel.cuh"
+
+void svtgpu_set_error(const char* fmt, const char* a, const char* b, int line);
+
+#define CK(call)                                                                              \
+    do {                                                                                      \
+        cudaError_t e_ = (call);                                                              \
+        if (e_ != cudaSuccess) {                                                              \
+            svtgpu_set_error("CUDA error: %s at %s (line %d)", cudaGetErrorString(e_), #call, \
+                             __LINE__);                                                       \
+            return SVTGPU_ERR_CUDA;                                                           \
+        }                                                                                     \
+    } while (0)
+
+struct SvtGpuContext {
+    static constexpr int kSide = 4;
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaStream_t side[kSide] = {};
+    cudaEvent_t side_done[kSide] = {};
+    cudaEvent_t fork = nullptr;
+    int16_t* d_iscan = nullptr;
+    int iscan_off[19][3] = {};
+    int16_t* d_qtables = nullptr;
+    int n_qrows = 0;
+    uint8_t* d_qm_wt = nullptr;
+    uint8_t* d_qm_iwt = nullptr;
+    int qm_off[2][19] = {};
+    long long launches = 0;
+};
+
+struct SvtGpuPlan {
+    SvtGpuContext* ctx = nullptr;
+    int n = 0;
+    svt::DevBlock* d_blocks = nullptr;
+    int first[19] = {};
+    int count[19] = {};
+    uint32_t max_qrow = 0;
+};
+
+// svtgpu_run plus the internal STAGE_FWD_FULL flag (used by the RTCD-level forward slots)
+int svtgpu_run_internal(SvtGpuContext* c, const SvtGpuPlan* pl, const SvtGpuBuffers* b, int stages,
+                        void* cuda_stream);

@@ -40,3 +40,23 @@ def load_qmatrices():
 
 def load_fused_vectors():
     return _npz("fused_vectors.npz")
+
+
+def build_tables(qt):
+    """[3*256][5][8] int16: rows plane*256 + qindex, from the golden quantizer tables of one bit
+    depth ({plane: [256][5][8]})."""
+    return np.ascontiguousarray(np.concatenate([qt[0], qt[1], qt[2]], axis=0))
+
+
+def qm_pack(qms, level):
+    """Concatenate the qmatrices of one level into (wt, iwt, off[2][19])."""
+    wt, iwt, off = [], [], np.zeros((2, 19), np.int32)
+    pos = 0
+    for pl in (0, 1):
+        for s in range(19):
+            w, iw = qms[(level, pl, s)]
+            off[pl, s] = pos
+            wt.append(w)
+            iwt.append(iw)
+            pos += len(w)
+    return np.concatenate(wt), np.concatenate(iwt), off

@@ -105,24 +105,7 @@ def aligned_copy(x, align=64):
 
 
 # ---- whole-batch runners (the checker side of the parity tests and of bench.py) -----------------
-def build_tables(qt):
-    """[3*256][5][8] int16: rows plane*256 + qindex, from the golden quantizer tables of one bit
-    depth ({plane: [256][5][8]})."""
-    return np.ascontiguousarray(np.concatenate([qt[0], qt[1], qt[2]], axis=0))
-
-
-def qm_pack(qms, level):
-    """Concatenate the qmatrices of one level into (wt, iwt, off[2][19])."""
-    wt, iwt, off = [], [], np.zeros((2, 19), np.int32)
-    pos = 0
-    for pl in (0, 1):
-        for s in range(19):
-            w, iw = qms[(level, pl, s)]
-            off[pl, s] = pos
-            wt.append(w)
-            iwt.append(iw)
-            pos += len(w)
-    return np.concatenate(wt), np.concatenate(iwt), off
+from golden_util import build_tables, qm_pack  # noqa: E402,F401  (fixture helpers)
 
 
 def _slices(n, threads):
@@ -191,3 +174,57 @@ def run_ref(batch, tables, threads=1, first=0, last=None, asm=1):
         [t.start() for t in th]
         [t.join() for t in th]
     return dict(qcoeff=q, dqcoeff=dq, eob=eob, energy=energy, recon=recon)
+
+
+class CpuRunner:
+    """Pre-allocated, repeatable CPU pass over a batch for timing (bench.py cpu_baseline and
+    --impl reference).  kind 'reference' = oracle/_ref (the reference's AVX2 RTCD path),
+    'port' = oracle/svt_oracle.c.  recon is updated in place pass after pass (same work)."""
+
+    def __init__(self, batch, tables, scans=None, qm=None, kind=None):
+        if kind is None:
+            kind = "reference" if (ref() is not None and qm is None) else "port"
+        self.kind, self.batch, self.qm = kind, batch, qm
+        self.tables = np.ascontiguousarray(tables)
+        n = batch.n_blocks
+        self.q = aligned(batch.n_coeff, np.int32)
+        self.dq = aligned(batch.n_coeff, np.int32)
+        self.eob = np.zeros(n, np.uint16)
+        self.energy = np.zeros(n, np.uint64)
+        self.recon = aligned_copy(batch.pred)
+        self.residual = aligned_copy(batch.residual)
+        self.blocks = np.ascontiguousarray(batch.blocks)
+        if kind == "port":
+            self.ptrs = (ctypes.c_void_p * (19 * 3))()
+            self.keep = []
+            for s in range(19):
+                for c in range(3):
+                    a = np.ascontiguousarray(scans[(s, c)][0])
+                    self.keep.append(a)
+                    self.ptrs[s * 3 + c] = a.ctypes.data
+
+    def _work(self, a, b):
+        if self.kind == "reference":
+            ref(1).ref_fused_blocks(P(self.blocks), a, b, P(self.residual), P(self.recon), P(self.tables),
+                                    P(self.q), P(self.dq), P(self.eob), P(self.energy))
+        else:
+            wt, iwt, off = self.qm if self.qm is not None else (None, None, None)
+            oracle().svto_fused_blocks(P(self.blocks), a, b, P(self.residual), P(self.recon),
+                                       P(self.tables), P(self.q), P(self.dq), P(self.eob), P(self.energy),
+                                       self.ptrs, 0, P(wt), P(iwt), P(off))
+
+    def run(self, threads):
+        """One pass; returns seconds."""
+        import threading
+        import time
+        # balance by samples, not block count
+        area = np.array(TX_W)[self.blocks["tx_size"]] * np.array(TX_H)[self.blocks["tx_size"]]
+        cum = np.cumsum(area)
+        cuts = [0] + [int(np.searchsorted(cum, cum[-1] * (i + 1) / threads)) + 1 for i in range(threads - 1)]
+        cuts.append(len(self.blocks))
+        cuts = sorted(set(min(c, len(self.blocks)) for c in cuts))
+        th = [threading.Thread(target=self._work, args=(cuts[i], cuts[i + 1])) for i in range(len(cuts) - 1)]
+        t0 = time.perf_counter()
+        [t.start() for t in th]
+        [t.join() for t in th]
+        return time.perf_counter() - t0
