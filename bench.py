@@ -220,6 +220,12 @@ def gpu_arm(args, rank, world, local_rank):
     total_samples = float(samples.item())
     value = total_samples * args.steps / (ms * 1e-3) / 1e6
 
+    if args.kernel_only:
+        if rank == 0:
+            print(json.dumps({"metric": METRIC, "value": value, "unit": UNIT, "ms_per_step": ms / args.steps,
+                              "gpu_launches": launches, "kernel_only": True}), flush=True)
+        return 0
+
     # ---- roofline of the dominant kernel, timed alone on the launching stream --------------------
     hbm, which = peaks()
     sizes = batch.blocks["tx_size"]
@@ -312,6 +318,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="1080p8", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--kernel-only", action="store_true",
+                    help="timed steps only (for ncu): no roofline sub-run, e2e or cpu_baseline")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
