@@ -125,47 +125,162 @@ SVT_HD constexpr int tx_id(int w, int h) {  // TxSize enum, EbDefinitions.h
     return -1;
 }
 
+// ---- CTA geometry and shared-memory layout --------------------------------------------------------
+//   buf   int32 [NB][BLK]      2-D transpose buffer; row pitch LD = W + 4 keeps every row 16-byte
+//                              aligned (128-bit row loads/stores) and conflict-free; block pitch
+//                              BLK == W (mod 32) keeps blocks that share a warp in disjoint banks
+//   stage int16 [NB][H][W]     residual staged by 128-bit coalesced copies (cp.async); after the
+//                              forward column pass the same bytes hold the prediction block and
+//                              then the reconstruction (pixels), copied back out 128 bits at a time
+//   isc   int32 [NCLS][KW*KH]  iscan + 1 of the scan classes this size can use
 template <int W, int H>
 struct Geo {
     static constexpr int TXS = tx_id(W, H);
     static constexpr int NT = 128;                    // threads per CTA
     static constexpr int NB = NT / cmin(W, H);        // blocks per CTA
-    static constexpr int LD = W + 1;                  // padded row pitch (words)
-    // block pitch == W (mod 32): blocks sharing a warp land in disjoint banks
+    static constexpr int LD = W + 4;
     static constexpr int BLK = ((H * LD - W + 31) / 32) * 32 + W;
     static constexpr int KW = cmin(W, 32), KH = cmin(H, 32);  // kept (coded) region
     static constexpr int LOG_SCALE = (W * H > 256) + (W * H > 1024);
     static constexpr bool RECT = (ilog2(W) - ilog2(H) == 1) || (ilog2(H) - ilog2(W) == 1);
-    static constexpr int SMEM_WORDS = NB * BLK;
+    static constexpr int NCLS = cmax(W, H) >= 32 ? 1 : 3;     // 32/64-point: DCT_DCT / IDTX only
+    static constexpr int BUF_WORDS = NB * BLK;
+    static constexpr int STAGE_WORDS = NB * W * H / 2;        // int16 per sample
+    static constexpr int ISC_WORDS = NCLS * KW * KH;
+    static constexpr int SMEM_BYTES = 4 * (BUF_WORDS + STAGE_WORDS + ISC_WORDS);
 };
 
-struct CtaShared {  // small per-CTA state next to the transpose buffer
+struct CtaShared {  // small per-CTA state next to the buffers above
     DevBlock blk[32];
     int eob[32];
     unsigned long long energy[32];
 };
 
-// ---- phase 1: forward column transforms -> shared (transposed hand-off) --------------------------
-template <int W, int H>
-SVT_HD void phase_fwd_col(const KParams& p, const DevBlock& d, int c, int* buf /* this block */) {
+// ---- staging copies ---------------------------------------------------------------------------------
+// rows x row_bytes between a strided global block and a dense shared block, `chunk` bytes at a
+// time (16, 8, 4, 2 or 1: the widest the addresses allow).  On the device the global->shared
+// direction uses cp.async (LDGSTS) for chunks >= 4 bytes, so the copy is in flight while the CTA
+// does other work; the host build is the plain loop.
+SVT_HD int align_chunk(size_t addr_bits, int row_bytes) {
+    int c = 16;
+    while (c > 1 && ((addr_bits | size_t(row_bytes)) & size_t(c - 1))) c >>= 1;
+    return c;
+}
+template <int CH>
+SVT_HD void copy_chunk(void* dst, const void* src) {
+    if constexpr (CH == 16) *static_cast<int4*>(dst) = *static_cast<const int4*>(src);
+    else if constexpr (CH == 8) *static_cast<long long*>(dst) = *static_cast<const long long*>(src);
+    else if constexpr (CH == 4) *static_cast<int*>(dst) = *static_cast<const int*>(src);
+    else if constexpr (CH == 2) *static_cast<short*>(dst) = *static_cast<const short*>(src);
+    else *static_cast<char*>(dst) = *static_cast<const char*>(src);
+}
+template <int CH>
+SVT_HD void g2s_chunk(void* smem_dst, const void* gsrc) {
+#if defined(__CUDA_ARCH__)
+    if constexpr (CH >= 4) {
+        const unsigned sa = static_cast<unsigned>(__cvta_generic_to_shared(smem_dst));
+        if constexpr (CH == 16)
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(sa), "l"(gsrc) : "memory");
+        else
+            asm volatile("cp.async.ca.shared.global [%0], [%1], %2;\n" ::"r"(sa), "l"(gsrc), "n"(CH) : "memory");
+        return;
+    }
+#endif
+    copy_chunk<CH>(smem_dst, gsrc);
+}
+SVT_HD void g2s_commit_wait() {
+#if defined(__CUDA_ARCH__)
+    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;\n" ::: "memory");
+#endif
+}
+// one block: global (strided) -> shared (dense); threads tid, tid + nthr, ... of the copy team
+template <int CH>
+SVT_HD void stage_in_t(char* sdst, const char* gsrc, int rows, int row_bytes, size_t gstride,
+                       int tid, int nthr) {
+    const int per_row = row_bytes / CH;
+    for (int i = tid; i < rows * per_row; i += nthr) {
+        const int r = i / per_row, k = i - r * per_row;
+        g2s_chunk<CH>(sdst + r * row_bytes + k * CH, gsrc + size_t(r) * gstride + k * CH);
+    }
+}
+template <int CH>
+SVT_HD void stage_out_t(char* gdst, const char* ssrc, int rows, int row_bytes, size_t gstride,
+                        int tid, int nthr) {
+    const int per_row = row_bytes / CH;
+    for (int i = tid; i < rows * per_row; i += nthr) {
+        const int r = i / per_row, k = i - r * per_row;
+        copy_chunk<CH>(gdst + size_t(r) * gstride + k * CH, ssrc + r * row_bytes + k * CH);
+    }
+}
+SVT_HD void stage_in(char* sdst, const char* gsrc, int rows, int row_bytes, size_t gstride, int tid,
+                     int nthr) {
+    switch (align_chunk(size_t(gsrc) | gstride, row_bytes)) {
+    case 16: stage_in_t<16>(sdst, gsrc, rows, row_bytes, gstride, tid, nthr); break;
+    case 8: stage_in_t<8>(sdst, gsrc, rows, row_bytes, gstride, tid, nthr); break;
+    case 4: stage_in_t<4>(sdst, gsrc, rows, row_bytes, gstride, tid, nthr); break;
+    case 2: stage_in_t<2>(sdst, gsrc, rows, row_bytes, gstride, tid, nthr); break;
+    default: stage_in_t<1>(sdst, gsrc, rows, row_bytes, gstride, tid, nthr); break;
+    }
+}
+SVT_HD void stage_out(char* gdst, const char* ssrc, int rows, int row_bytes, size_t gstride, int tid,
+                      int nthr) {
+    switch (align_chunk(size_t(gdst) | gstride, row_bytes)) {
+    case 16: stage_out_t<16>(gdst, ssrc, rows, row_bytes, gstride, tid, nthr); break;
+    case 8: stage_out_t<8>(gdst, ssrc, rows, row_bytes, gstride, tid, nthr); break;
+    case 4: stage_out_t<4>(gdst, ssrc, rows, row_bytes, gstride, tid, nthr); break;
+    case 2: stage_out_t<2>(gdst, ssrc, rows, row_bytes, gstride, tid, nthr); break;
+    default: stage_out_t<1>(gdst, ssrc, rows, row_bytes, gstride, tid, nthr); break;
+    }
+}
+
+// ---- 1-D dispatch with the kind as a template argument ----------------------------------------------
+// Each variant contains its own loads and stores, so the three kinds never merge register state.
+template <int N, int BIT, int KIND>
+SVT_HD void fwd1d_k(int (&x)[N]) {
+    if constexpr (KIND == 0) fdct<N, BIT>(x);
+    else if constexpr (KIND == 1) fadst<N, BIT>(x);
+    else identity<N>(x);
+}
+template <int N, int KIND, class K>
+SVT_HD void inv1d_k(int (&x)[N], K k) {
+    if constexpr (KIND == 0) idct<N, 12>(x, k);
+    else if constexpr (KIND == 1) iadst<N, 12>(x, k);
+    else identity<N>(x);
+}
+
+// ---- phase 1: forward column transform, staged residual -> transpose buffer ------------------------
+template <int W, int H, int KIND>
+SVT_HD void fwd_col_k(const DevBlock& d, int c, int* buf, const int16_t* res) {
     using G = Geo<W, H>;
     constexpr int S0 = fwd_shift(W, H, 0), S1 = -fwd_shift(W, H, 1);
     const int t = d.meta & META_TYPE_MASK;
-    const int vt = vtx_of(t), ht = htx_of(t);
-    const bool ud = vt == 2, lr = ht == 2;
-    const int16_t* src = p.residual + d.res_off + c;
+    const bool ud = vtx_of(t) == 2, lr = htx_of(t) == 2;
     int x[H];
+    if (ud) {  // flip upside down, EbTransforms.c:3739-3744
 #pragma unroll
-    for (int r = 0; r < H; ++r) {
-        const int rr = ud ? H - 1 - r : r;
-        x[r] = int(src[size_t(rr) * d.res_stride]) * (1 << S0);
+        for (int r = 0; r < H; ++r) x[r] = int(res[(H - 1 - r) * W + c]) * (1 << S0);
+    } else {
+#pragma unroll
+        for (int r = 0; r < H; ++r) x[r] = int(res[r * W + c]) * (1 << S0);
     }
-    fwd1d<H, fwd_cos_col(W, H)>(x, kind_of(vt));
-    const int cc = lr ? W - 1 - c : c;
+    fwd1d_k<H, fwd_cos_col(W, H), KIND>(x);
+    int* dst = buf + (lr ? W - 1 - c : c);  // flip left to right, EbTransforms.c:3752-3757
 #pragma unroll
     for (int r = 0; r < H; ++r) {
         if constexpr (S1 > 0) x[r] = rshift<(S1 > 0 ? S1 : 1)>(x[r]);
-        buf[r * G::LD + cc] = x[r];
+        dst[r * G::LD] = x[r];
+    }
+}
+template <int W, int H>
+SVT_HD void phase_fwd_col(const DevBlock& d, int c, int* buf, const int16_t* res) {
+    const int kind = kind_of(vtx_of(d.meta & META_TYPE_MASK));
+    if constexpr (H == 64) fwd_col_k<W, H, 0>(d, c, buf, res);
+    else if constexpr (H == 32) {
+        if (kind == 2) fwd_col_k<W, H, 2>(d, c, buf, res); else fwd_col_k<W, H, 0>(d, c, buf, res);
+    } else {
+        if (kind == 0) fwd_col_k<W, H, 0>(d, c, buf, res);
+        else if (kind == 1) fwd_col_k<W, H, 1>(d, c, buf, res);
+        else fwd_col_k<W, H, 2>(d, c, buf, res);
     }
 }
 
@@ -184,50 +299,56 @@ SVT_HD QRow load_qrow(const int16_t* t) {
 // flat (no qmatrix): aom_highbd_quantize_b*_avx2 arithmetic
 // (Source/Lib/Common/ASM_AVX2/highbd_quantize_intrin_avx2.c:80-125), equal to
 // highbd_quantize_b_helper_c (EbFullLoop.c:239) for the tables av1_build_quantizer produces.
+// Branch-free: the level is computed for every position and zeroed below zbin.  t1max is 32767
+// for the 8-bit C variant (EbFullLoop.c:86-88) and INT_MAX otherwise.  Returns |level|.
 template <int LOG_SCALE>
-SVT_HD void quant_flat(int cf, const QSet& q, bool clamp16, int& qc, int& dqc) {
-    const int sign = cf >> 31;
-    const int ab = (cf ^ sign) - sign;
-    qc = 0; dqc = 0;
-    if (ab >= q.zbin) {
-        int t1 = ab + q.round;
-        if (clamp16) t1 = t1 > 32767 ? 32767 : t1;  // 8-bit C variant, EbFullLoop.c:86-88
-        const int64_t p1 = int64_t(t1) * q.quant;
-        const uint32_t t2 = uint32_t(uint64_t(p1) >> 16) + uint32_t(t1);
-        const uint64_t p2 = uint64_t(t2) * uint32_t(q.qshift);
-        const int aq = int(uint32_t(p2 >> (16 - LOG_SCALE)));
+SVT_HD int quant_flat(int cf, const QSet& q, int t1max, int& qc, int& dqc) {
+    const int sgn = (cf >> 31) | 1;
+    const int ab = cf < 0 ? -cf : cf;
+    int t1 = ab + q.round;
+    t1 = t1 > t1max ? t1max : t1;
+    const int64_t p1 = int64_t(t1) * q.quant;
+    const uint32_t t2 = uint32_t(uint64_t(p1) >> 16) + uint32_t(t1);
+    const uint64_t p2 = uint64_t(t2) * uint32_t(q.qshift);
+    int aq = int(uint32_t(p2 >> (16 - LOG_SCALE)));
+    aq = ab >= q.zbin ? aq : 0;
+    qc = int(unsigned(aq) * unsigned(sgn));
+    if constexpr (LOG_SCALE == 0) {
+        dqc = int(unsigned(qc) * unsigned(q.dequant));
+    } else {
         const int adq = int(unsigned(aq) * unsigned(q.dequant)) >> LOG_SCALE;
-        qc = (aq ^ sign) - sign;
-        dqc = (adq ^ sign) - sign;
+        dqc = int(unsigned(adq) * unsigned(sgn));
     }
+    return aq;
 }
 // with quantization matrices: highbd_quantize_b_helper_c, EbFullLoop.c:239-296
 template <int LOG_SCALE>
-SVT_HD void quant_qm(int cf, const QSet& q, int wt, int iwt, int& qc, int& dqc) {
+SVT_HD int quant_qm(int cf, const QSet& q, int wt, int iwt, int& qc, int& dqc) {
     const int sign = cf >> 31;
     const int ab = (cf ^ sign) - sign;
     const int cw = int(unsigned(cf) * unsigned(wt));
     qc = 0; dqc = 0;
+    int aq = 0;
     if (cw >= q.zbin * 32 || cw <= -q.zbin * 32) {
         const int64_t tw = (int64_t(ab) + q.round) * wt;
         const int64_t t2 = ((tw * q.quant) >> 16) + tw;
-        const int aq = int((t2 * q.qshift) >> (16 - LOG_SCALE + 5));
+        aq = int((t2 * q.qshift) >> (16 - LOG_SCALE + 5));
         const int dq = (q.dequant * iwt + 16) >> 5;
         const int adq = int(unsigned(aq) * unsigned(dq)) >> LOG_SCALE;
         qc = (aq ^ sign) - sign;
         dqc = (adq ^ sign) - sign;
     }
+    return aq;
 }
 
-// ---- phase 2: forward row -> (energy, pack) -> quantize -> inverse row -> shared ------------------
-// Returns this row's eob candidate and discarded-region energy.
-template <int W, int H>
-SVT_HD void phase_row(const KParams& p, const DevBlock& d, int r, int* buf, int& eob_max,
-                      unsigned long long& energy_sum) {
+// ---- phase 2: forward row -> (energy, pack) -> quantize -> inverse row, all on one thread's registers
+// isc: this block's (iscan + 1) table in shared memory.  Returns the row's eob candidate and
+// discarded-region energy.
+template <int W, int H, int KIND>
+SVT_HD void row_k(const KParams& p, const DevBlock& d, int r, int* buf, const int* isc, int& eob_max,
+                  unsigned long long& energy_sum) {
     using G = Geo<W, H>;
     constexpr int KW = G::KW, KH = G::KH, LS = G::LOG_SCALE;
-    const int t = d.meta & META_TYPE_MASK;
-    const int ht = htx_of(t);
     const bool bd10 = d.meta & META_BD10;
     int* row = buf + r * G::LD;
     int x[W];
@@ -237,8 +358,11 @@ SVT_HD void phase_row(const KParams& p, const DevBlock& d, int r, int* buf, int&
 
     if (p.stages & STAGE_FWD) {
 #pragma unroll
-        for (int c = 0; c < W; ++c) x[c] = row[c];
-        fwd1d<W, fwd_cos_row(W, H)>(x, kind_of(ht));
+        for (int c = 0; c < W; c += 4) {
+            const int4 v = *reinterpret_cast<const int4*>(row + c);
+            x[c] = v.x; x[c + 1] = v.y; x[c + 2] = v.z; x[c + 3] = v.w;
+        }
+        fwd1d_k<W, fwd_cos_row(W, H), KIND>(x);
         constexpr int S2 = -fwd_shift(W, H, 2);
 #pragma unroll
         for (int c = 0; c < W; ++c) {
@@ -272,90 +396,185 @@ SVT_HD void phase_row(const KParams& p, const DevBlock& d, int r, int* buf, int&
 
     if ((p.stages & STAGE_QUANT) && r < KH) {
         const QRow q = load_qrow<LS>(p.qtables + size_t(d.qrow) * 40);
-        const QSet q0 = r == 0 ? q.dc : q.ac;
-        const int cls = t < 10 ? 0 : ((t & 1) ? 2 : 1);  // av1_scan_orders, EbTransforms.h:3349
-        const int16_t* iscan = p.iscan + p.iscan_off[G::TXS][cls] + r * KW;
-        const bool clamp16 = d.meta & META_CLAMP16;
+        const QSet q0 = r == 0 ? q.dc : q.ac;  // position 0 of the block is DC
+        const int t1max = (d.meta & META_CLAMP16) ? 32767 : 0x7fffffff;
         const bool use_qm = (d.meta & META_USE_QM) && p.qm_wt != nullptr;
-        const int qmo = p.qm_off[((d.meta >> META_PLANE_SHIFT) & 3) > 0][G::TXS] + r * KW;
+        const int* krow = isc + r * KW;
         int e = 0;
+        if (!use_qm) {
 #pragma unroll
-        for (int c0 = 0; c0 < KW; c0 += 4) {
-            int qv[4];
+            for (int c0 = 0; c0 < KW; c0 += 4) {
+                const int4 key = *reinterpret_cast<const int4*>(krow + c0);
+                const int kk[4] = { key.x, key.y, key.z, key.w };
+                int qv[4];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const int c = c0 + j;
-                int dqc;
-                const QSet& qs = (c == 0) ? q0 : q.ac;  // position 0 of the block is DC
-                if (!use_qm) quant_flat<LS>(x[c], qs, clamp16, qv[j], dqc);
-                else quant_qm<LS>(x[c], qs, p.qm_wt[qmo + c], p.qm_iwt[qmo + c], qv[j], dqc);
-                x[c] = dqc;
-                if (qv[j] != 0) { const int s = int(iscan[c]) + 1; e = s > e ? s : e; }
+                for (int j = 0; j < 4; ++j) {
+                    const int c = c0 + j;
+                    int dqc;
+                    const int aq = quant_flat<LS>(x[c], c == 0 ? q0 : q.ac, t1max, qv[j], dqc);
+                    x[c] = dqc;
+                    const int cand = aq != 0 ? kk[j] : 0;
+                    e = cand > e ? cand : e;
+                }
+                *reinterpret_cast<int4*>(p.qcoeff + cbase + c0) = make_int4(qv[0], qv[1], qv[2], qv[3]);
+                *reinterpret_cast<int4*>(p.dqcoeff + cbase + c0) =
+                    make_int4(x[c0], x[c0 + 1], x[c0 + 2], x[c0 + 3]);
             }
-            *reinterpret_cast<int4*>(p.qcoeff + cbase + c0) = make_int4(qv[0], qv[1], qv[2], qv[3]);
-            *reinterpret_cast<int4*>(p.dqcoeff + cbase + c0) =
-                make_int4(x[c0], x[c0 + 1], x[c0 + 2], x[c0 + 3]);
+        } else {
+            const int qmo = p.qm_off[((d.meta >> META_PLANE_SHIFT) & 3) > 0][G::TXS] + r * KW;
+#pragma unroll
+            for (int c0 = 0; c0 < KW; c0 += 4) {
+                int qv[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int c = c0 + j;
+                    int dqc;
+                    const int aq = quant_qm<LS>(x[c], c == 0 ? q0 : q.ac, p.qm_wt[qmo + c],
+                                                p.qm_iwt[qmo + c], qv[j], dqc);
+                    x[c] = dqc;
+                    const int cand = aq != 0 ? krow[c] : 0;
+                    e = cand > e ? cand : e;
+                }
+                *reinterpret_cast<int4*>(p.qcoeff + cbase + c0) = make_int4(qv[0], qv[1], qv[2], qv[3]);
+                *reinterpret_cast<int4*>(p.dqcoeff + cbase + c0) =
+                    make_int4(x[c0], x[c0 + 1], x[c0 + 2], x[c0 + 3]);
+            }
         }
         eob_max = e;
     }
 
     if (p.stages & STAGE_INV) {  // inv_txfm2d_add_c row pass, EbTransforms.c:8215-8236
         if (r < KH) {
-            const Clamp kin(bd10 ? 18 : 16);   // clamp_buf(bd + 8)
-            const Clamp krow(bd10 ? 18 : 16);  // av1_gen_inv_stage_range rows: 16 / 18
+            const Clamp krow_c(bd10 ? 18 : 16);  // clamp_buf(bd + 8) and the row stage range: 16 / 18
 #pragma unroll
             for (int c = 0; c < W; ++c) {
                 if (c >= KW) x[c] = 0;  // 64-wide: re-expansion with zeros, EbTransforms.c:8299
                 else {
                     if constexpr (G::RECT) x[c] = mul_round12(x[c], 2896);
-                    x[c] = kin(x[c]);
+                    x[c] = krow_c(x[c]);
                 }
             }
-            inv1d<W>(x, kind_of(ht), krow);
+            inv1d_k<W, KIND>(x, krow_c);
             constexpr int IS0 = inv_shift0(W, H);
 #pragma unroll
-            for (int c = 0; c < W; ++c) {
-                if constexpr (IS0 > 0) x[c] = rshift<(IS0 > 0 ? IS0 : 1)>(x[c]);
-                row[c] = x[c];
+            for (int c = 0; c < W; c += 4) {
+                if constexpr (IS0 > 0) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) x[c + j] = rshift<(IS0 > 0 ? IS0 : 1)>(x[c + j]);
+                }
+                *reinterpret_cast<int4*>(row + c) = make_int4(x[c], x[c + 1], x[c + 2], x[c + 3]);
             }
         } else {
 #pragma unroll
-            for (int c = 0; c < W; ++c) row[c] = 0;
+            for (int c = 0; c < W; c += 4) *reinterpret_cast<int4*>(row + c) = make_int4(0, 0, 0, 0);
         }
     }
 }
-
-// ---- phase 3: inverse column transforms + reconstruction ------------------------------------------
 template <int W, int H>
-SVT_HD void phase_inv_col(const KParams& p, const DevBlock& d, int c, const int* buf) {
+SVT_HD void phase_row(const KParams& p, const DevBlock& d, int r, int* buf, const int* isc, int& e,
+                      unsigned long long& en) {
+    const int kind = kind_of(htx_of(d.meta & META_TYPE_MASK));
+    if constexpr (W == 64) row_k<W, H, 0>(p, d, r, buf, isc, e, en);
+    else if constexpr (W == 32) {
+        if (kind == 2) row_k<W, H, 2>(p, d, r, buf, isc, e, en); else row_k<W, H, 0>(p, d, r, buf, isc, e, en);
+    } else {
+        if (kind == 0) row_k<W, H, 0>(p, d, r, buf, isc, e, en);
+        else if (kind == 1) row_k<W, H, 1>(p, d, r, buf, isc, e, en);
+        else row_k<W, H, 2>(p, d, r, buf, isc, e, en);
+    }
+}
+
+// ---- phase 3: inverse column transform + reconstruction on the staged prediction block --------------
+// pix: the block's prediction pixels in shared memory (dense, W per row), overwritten in place with
+// the reconstruction (highbd_clip_pixel_add + check_range, EbTransforms.c:7794-7813).
+template <int W, int H, int KIND, class PIX>
+SVT_HD void inv_col_k(const DevBlock& d, int c, const int* buf, PIX* pix, int pmax, int rmax) {
     using G = Geo<W, H>;
     const int t = d.meta & META_TYPE_MASK;
-    const int vt = vtx_of(t), ht = htx_of(t);
-    const bool ud = vt == 2, lr = ht == 2;
-    const bool bd10 = d.meta & META_BD10;
-    const int cc = lr ? W - 1 - c : c;
-    const Clamp kmid(16);  // clamp_buf(max(bd + 6, 16)) == 16 for bd 8 and 10
-    const Clamp kcol(16);  // av1_gen_inv_stage_range columns
+    const bool ud = vtx_of(t) == 2, lr = htx_of(t) == 2;
+    const int* src = buf + (lr ? W - 1 - c : c);
+    const Clamp k16(16);  // clamp_buf(max(bd + 6, 16)) and the column stage range: 16 for bd 8 / 10
     int x[H];
 #pragma unroll
-    for (int r = 0; r < H; ++r) x[r] = kmid(buf[r * G::LD + cc]);
-    inv1d<H>(x, kind_of(vt), kcol);
-    // highbd_clip_pixel_add + check_range, EbTransforms.c:7794-7813
-    const int pmax = bd10 ? 1023 : 255;
-    const int rmax = bd10 ? ((1 << 17) - 1 + (914 << 3)) : ((1 << 15) - 1 + (914 << 1));
-    const size_t o = size_t(d.rec_off) + c;
+    for (int r = 0; r < H; ++r) x[r] = k16(src[r * G::LD]);
+    inv1d_k<H, KIND>(x, k16);
 #pragma unroll
     for (int r = 0; r < H; ++r) {
-        int v = rshift<4>(x[ud ? H - 1 - r : r]);
+        int v = rshift<4>(x[r]);
         v = v > rmax ? rmax : (v < -rmax - 1 ? -rmax - 1 : v);
-        const size_t a = o + size_t(r) * d.rec_stride;
-        int px = bd10 ? int(static_cast<const uint16_t*>(p.pred)[a])
-                      : int(static_cast<const uint8_t*>(p.pred)[a]);
-        px += v;
-        px = px < 0 ? 0 : (px > pmax ? pmax : px);
-        if (bd10) static_cast<uint16_t*>(p.recon)[a] = uint16_t(px);
-        else static_cast<uint8_t*>(p.recon)[a] = uint8_t(px);
+        x[r] = v;
     }
+    if (ud) {  // flip upside down, EbTransforms.c:8258-8264
+#pragma unroll
+        for (int r = 0; r < H; ++r) {
+            PIX* q = pix + (H - 1 - r) * W + c;
+            const int px = int(*q) + x[r];
+            *q = PIX(px < 0 ? 0 : (px > pmax ? pmax : px));
+        }
+    } else {
+#pragma unroll
+        for (int r = 0; r < H; ++r) {
+            PIX* q = pix + r * W + c;
+            const int px = int(*q) + x[r];
+            *q = PIX(px < 0 ? 0 : (px > pmax ? pmax : px));
+        }
+    }
+}
+template <int W, int H, int KIND>
+SVT_HD void inv_col_bd(const DevBlock& d, int c, const int* buf, void* pix) {
+    if (d.meta & META_BD10)
+        inv_col_k<W, H, KIND>(d, c, buf, static_cast<uint16_t*>(pix), 1023, (1 << 17) - 1 + (914 << 3));
+    else
+        inv_col_k<W, H, KIND>(d, c, buf, static_cast<uint8_t*>(pix), 255, (1 << 15) - 1 + (914 << 1));
+}
+template <int W, int H>
+SVT_HD void phase_inv_col(const DevBlock& d, int c, const int* buf, void* pix) {
+    const int kind = kind_of(vtx_of(d.meta & META_TYPE_MASK));
+    if constexpr (H == 64) inv_col_bd<W, H, 0>(d, c, buf, pix);
+    else if constexpr (H == 32) {
+        if (kind == 2) inv_col_bd<W, H, 2>(d, c, buf, pix); else inv_col_bd<W, H, 0>(d, c, buf, pix);
+    } else {
+        if (kind == 0) inv_col_bd<W, H, 0>(d, c, buf, pix);
+        else if (kind == 1) inv_col_bd<W, H, 1>(d, c, buf, pix);
+        else inv_col_bd<W, H, 2>(d, c, buf, pix);
+    }
+}
+
+// ---- per-block staging steps shared by the kernel and the host emulation ---------------------------
+SVT_HD int px_bytes(const DevBlock& d) { return (d.meta & META_BD10) ? 2 : 1; }
+template <int W, int H>
+SVT_HD void stage_residual(const KParams& p, const DevBlock& d, int16_t* sres, int tid, int nthr) {
+    stage_in(reinterpret_cast<char*>(sres), reinterpret_cast<const char*>(p.residual + d.res_off), H,
+             W * 2, size_t(d.res_stride) * 2, tid, nthr);
+}
+template <int W, int H>
+SVT_HD void stage_pred(const KParams& p, const DevBlock& d, void* spix, int tid, int nthr) {
+    const int pb = px_bytes(d);
+    stage_in(static_cast<char*>(spix), static_cast<const char*>(p.pred) + size_t(d.rec_off) * pb, H,
+             W * pb, size_t(d.rec_stride) * pb, tid, nthr);
+}
+template <int W, int H>
+SVT_HD void unstage_recon(const KParams& p, const DevBlock& d, const void* spix, int tid, int nthr) {
+    const int pb = px_bytes(d);
+    stage_out(static_cast<char*>(p.recon) + size_t(d.rec_off) * pb, static_cast<const char*>(spix), H,
+              W * pb, size_t(d.rec_stride) * pb, tid, nthr);
+}
+// (iscan + 1) of the classes this size can use, as int32
+template <int W, int H>
+SVT_HD void stage_iscan(const KParams& p, int* sisc, int tid, int nthr) {
+    using G = Geo<W, H>;
+    constexpr int N = G::KW * G::KH;
+    for (int i = tid; i < G::NCLS * N; i += nthr) {
+        const int cls = i / N;
+        sisc[i] = int(p.iscan[p.iscan_off[G::TXS][cls] + (i - cls * N)]) + 1;
+    }
+}
+template <int W, int H>
+SVT_HD const int* block_iscan(const DevBlock& d, const int* sisc) {
+    using G = Geo<W, H>;
+    const int t = d.meta & META_TYPE_MASK;
+    const int cls = t < 10 ? 0 : ((t & 1) ? 2 : 1);  // av1_scan_orders, EbTransforms.h:3349
+    return sisc + (G::NCLS == 1 ? 0 : cls) * (G::KW * G::KH);
 }
 
 #if defined(__CUDACC__)
@@ -363,7 +582,10 @@ template <int W, int H>
 __global__ void __launch_bounds__(Geo<W, H>::NT)
 residual_kernel(const __grid_constant__ KParams p, int first_block, int count) {
     using G = Geo<W, H>;
-    __shared__ int buf[G::SMEM_WORDS];
+    extern __shared__ __align__(16) int smem[];
+    int* buf = smem;
+    int16_t* stage = reinterpret_cast<int16_t*>(smem + G::BUF_WORDS);
+    int* sisc = smem + G::BUF_WORDS + G::STAGE_WORDS;
     __shared__ CtaShared sh;
     const int tid = threadIdx.x;
     const int base = first_block + blockIdx.x * G::NB;
@@ -374,23 +596,38 @@ residual_kernel(const __grid_constant__ KParams p, int first_block, int count) {
         sh.energy[tid] = 0ull;
     }
     __syncthreads();
+    // copy teams: TPB consecutive threads move one block's rows, 16 bytes per thread per step
+    constexpr int TPB = G::NT / G::NB;
+    const int tb = tid / TPB, tl = tid - tb * TPB;
+    int16_t* my_stage = stage + tb * (W * H);
     if (p.stages & STAGE_FWD) {
+        if (tb < nb) stage_residual<W, H>(p, sh.blk[tb], my_stage, tl, TPB);
+        if (p.stages & STAGE_QUANT) stage_iscan<W, H>(p, sisc, tid, G::NT);
+        g2s_commit_wait();
+        __syncthreads();
         for (int task = tid; task < G::NB * W; task += G::NT) {
             const int b = task / W, c = task % W;
-            if (b < nb) phase_fwd_col<W, H>(p, sh.blk[b], c, buf + b * G::BLK);
+            if (b < nb) phase_fwd_col<W, H>(sh.blk[b], c, buf + b * G::BLK, stage + b * (W * H));
         }
         __syncthreads();
+    } else if (p.stages & STAGE_QUANT) {
+        stage_iscan<W, H>(p, sisc, tid, G::NT);
+        __syncthreads();
     }
+    // the residual is consumed: the prediction block streams into the same bytes while the row
+    // phase runs
+    if ((p.stages & STAGE_INV) && tb < nb) stage_pred<W, H>(p, sh.blk[tb], my_stage, tl, TPB);
     for (int task = tid; task < G::NB * H; task += G::NT) {
         const int b = task / H, r = task % H;
         if (b < nb) {
             int e;
             unsigned long long en;
-            phase_row<W, H>(p, sh.blk[b], r, buf + b * G::BLK, e, en);
+            phase_row<W, H>(p, sh.blk[b], r, buf + b * G::BLK, block_iscan<W, H>(sh.blk[b], sisc), e, en);
             if (e) atomicMax(&sh.eob[b], e);
             if (G::KW != W || G::KH != H) { if (en) atomicAdd(&sh.energy[b], en); }
         }
     }
+    g2s_commit_wait();
     __syncthreads();
     if (tid < nb) {
         if (p.stages & STAGE_QUANT) p.eob[sh.blk[tid].id] = uint16_t(sh.eob[tid]);
@@ -399,8 +636,10 @@ residual_kernel(const __grid_constant__ KParams p, int first_block, int count) {
     if (p.stages & STAGE_INV) {
         for (int task = tid; task < G::NB * W; task += G::NT) {
             const int b = task / W, c = task % W;
-            if (b < nb) phase_inv_col<W, H>(p, sh.blk[b], c, buf + b * G::BLK);
+            if (b < nb) phase_inv_col<W, H>(sh.blk[b], c, buf + b * G::BLK, stage + b * (W * H));
         }
+        __syncthreads();
+        if (tb < nb) unstage_recon<W, H>(p, sh.blk[tb], my_stage, tl, TPB);
     }
 }
 
@@ -420,10 +659,10 @@ quant_kernel(const int32_t* coeff, int n, const int16_t* tab /* 5 x {DC, AC} */,
     int e = 0;
     for (int i = threadIdx.x; i < n; i += blockDim.x) {
         int qc, dqc;
-        quant_flat<LOG_SCALE>(coeff[i], i == 0 ? dc : ac, false, qc, dqc);
+        const int aq = quant_flat<LOG_SCALE>(coeff[i], i == 0 ? dc : ac, 0x7fffffff, qc, dqc);
         qcoeff[i] = qc;
         dqcoeff[i] = dqc;
-        if (qc != 0) { const int s = int(iscan[i]) + 1; e = s > e ? s : e; }
+        if (aq != 0) { const int s = int(iscan[i]) + 1; e = s > e ? s : e; }
     }
     if (e) atomicMax(&s_eob, e);
     __syncthreads();

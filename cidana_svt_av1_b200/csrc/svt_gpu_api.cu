@@ -28,8 +28,17 @@ extern "C" const char* svtgpu_last_error(void) { return g_err; }
 template <int W, int H>
 static cudaError_t launch_size(const KParams& p, int first, int count, cudaStream_t st) {
     using G = Geo<W, H>;
+    static bool configured[64] = {};  // per device: opt in to > 48 KB of dynamic shared memory
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!configured[dev & 63]) {
+        cudaError_t e = cudaFuncSetAttribute(residual_kernel<W, H>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES);
+        if (e != cudaSuccess) return e;
+        configured[dev & 63] = true;
+    }
     const int grid = (count + G::NB - 1) / G::NB;
-    residual_kernel<W, H><<<grid, G::NT, 0, st>>>(p, first, count);
+    residual_kernel<W, H><<<grid, G::NT, G::SMEM_BYTES, st>>>(p, first, count);
     return cudaGetLastError();
 }
 static cudaError_t launch_bucket(int tx_size, const KParams& p, int first, int count, cudaStream_t st) {

@@ -73,11 +73,30 @@ SVT_HD int rshift(int v) { return int(unsigned(v) + (1u << (BIT - 1))) >> BIT; }
 
 // Clamp policy: forward transforms do not clamp; inverse transforms clamp every add/sub to the
 // stage range (16 or 18 bits, av1_gen_inv_stage_range EbTransforms.c:5404).
-struct NoClamp { SVT_HD int operator()(int v) const { return v; } };
+struct NoClamp {
+    SVT_HD int operator()(int v) const { return v; }
+    SVT_HD int add(int a, int b) const { return int(unsigned(a) + unsigned(b)); }
+    SVT_HD int sub(int a, int b) const { return int(unsigned(a) - unsigned(b)); }
+};
 struct Clamp {
     int lo, hi;
     SVT_HD explicit Clamp(int bits) : lo(-(1 << (bits - 1))), hi((1 << (bits - 1)) - 1) {}
     SVT_HD int operator()(int v) const { return v < lo ? lo : (v > hi ? hi : v); }
+    // clamp(a +- b): on sm_100a the add and the first bound fuse into one VIADDMNMX
+    SVT_HD int add(int a, int b) const {
+#if defined(__CUDA_ARCH__)
+        return min(__viaddmax_s32(a, b, lo), hi);
+#else
+        return (*this)(a + b);
+#endif
+    }
+    SVT_HD int sub(int a, int b) const {
+#if defined(__CUDA_ARCH__)
+        return min(__viaddmax_s32(a, -b, lo), hi);
+#else
+        return (*this)(a - b);
+#endif
+    }
 };
 
 #define SVT_C(j) (kCos.v[BIT - 10][(j)])
@@ -92,8 +111,8 @@ SVT_HD void odd_bfly(int* y, K k) {
         for (int i = 0; i < W / 2; ++i) {
             const int ia = g * W + i, ib = g * W + W - 1 - i;
             const int a = y[ia], b = y[ib];
-            if (g & 1) { y[ia] = k(b - a); y[ib] = k(b + a); }
-            else       { y[ia] = k(a + b); y[ib] = k(a - b); }
+            if (g & 1) { y[ia] = k.sub(b, a); y[ib] = k.add(b, a); }
+            else       { y[ia] = k.add(a, b); y[ib] = k.sub(a, b); }
         }
 }
 template <int M, int W, int BIT, bool INV>
@@ -202,8 +221,8 @@ template <int N, int BIT> struct Dct {
 #pragma unroll
         for (int i = 0; i < N / 2; ++i) {
             const int a = x[i], b = x[N - 1 - i];
-            x[i] = k(a + b);
-            x[N - 1 - i] = k(a - b);
+            x[i] = k.add(a, b);
+            x[N - 1 - i] = k.sub(a, b);
         }
     }
 };
@@ -273,8 +292,8 @@ SVT_HD void adst_bfly(int* x, K k) {
 #pragma unroll
         for (int i = 0; i < S; ++i) {
             const int a = x[g + i], b = x[g + i + S];
-            x[g + i] = k(a + b);
-            x[g + i + S] = k(a - b);
+            x[g + i] = k.add(a, b);
+            x[g + i + S] = k.sub(a, b);
         }
 }
 template <int N, int BIT>

@@ -10,22 +10,30 @@ template <int W, int H>
 static void run_size(const KParams& p, int first, int count) {
     using G = Geo<W, H>;
     std::vector<int> buf(G::BLK);
+    std::vector<int> isc(G::ISC_WORDS);
+    alignas(16) static thread_local int16_t stage[64 * 64];
+    if (p.stages & STAGE_QUANT) stage_iscan<W, H>(p, isc.data(), 0, 1);
     for (int i = first; i < first + count; ++i) {
         const DevBlock& d = p.blocks[i];
-        if (p.stages & STAGE_FWD)
-            for (int c = 0; c < W; ++c) phase_fwd_col<W, H>(p, d, c, buf.data());
+        if (p.stages & STAGE_FWD) {
+            stage_residual<W, H>(p, d, stage, 0, 1);
+            for (int c = 0; c < W; ++c) phase_fwd_col<W, H>(d, c, buf.data(), stage);
+        }
+        if (p.stages & STAGE_INV) stage_pred<W, H>(p, d, stage, 0, 1);
         int eob = 0;
         unsigned long long energy = 0;
         for (int r = 0; r < H; ++r) {
             int e; unsigned long long en;
-            phase_row<W, H>(p, d, r, buf.data(), e, en);
+            phase_row<W, H>(p, d, r, buf.data(), block_iscan<W, H>(d, isc.data()), e, en);
             eob = e > eob ? e : eob;
             energy += en;
         }
         if (p.stages & STAGE_QUANT) p.eob[d.id] = (uint16_t)eob;
         if ((p.stages & STAGE_FWD) && p.energy) p.energy[d.id] = energy;
-        if (p.stages & STAGE_INV)
-            for (int c = 0; c < W; ++c) phase_inv_col<W, H>(p, d, c, buf.data());
+        if (p.stages & STAGE_INV) {
+            for (int c = 0; c < W; ++c) phase_inv_col<W, H>(d, c, buf.data(), stage);
+            unstage_recon<W, H>(p, d, stage, 0, 1);
+        }
     }
 }
 
