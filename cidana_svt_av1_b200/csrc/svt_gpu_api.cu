@@ -25,21 +25,27 @@ void svtgpu_set_error(const char* fmt, const char* a, const char* b, int line) {
 extern "C" const char* svtgpu_last_error(void) { return g_err; }
 
 // ---- launches ------------------------------------------------------------------------------------
-template <int W, int H>
-static cudaError_t launch_size(const KParams& p, int first, int count, cudaStream_t st) {
+template <int W, int H, bool QM>
+static cudaError_t launch_size_q(const KParams& p, int first, int count, cudaStream_t st) {
     using G = Geo<W, H>;
     static bool configured[64] = {};  // per device: opt in to > 48 KB of dynamic shared memory
     int dev = 0;
     cudaGetDevice(&dev);
     if (!configured[dev & 63]) {
-        cudaError_t e = cudaFuncSetAttribute(residual_kernel<W, H>,
+        cudaError_t e = cudaFuncSetAttribute(residual_kernel<W, H, QM>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES);
         if (e != cudaSuccess) return e;
         configured[dev & 63] = true;
     }
     const int grid = (count + G::NB - 1) / G::NB;
-    residual_kernel<W, H><<<grid, G::NT, G::SMEM_BYTES, st>>>(p, first, count);
+    residual_kernel<W, H, QM><<<grid, G::NT, G::SMEM_BYTES, st>>>(p, first, count);
     return cudaGetLastError();
+}
+template <int W, int H>
+static cudaError_t launch_size(const KParams& p, int first, int count, cudaStream_t st) {
+    // the qmatrix variant carries the 64-bit quantizer; keep it out of the common instruction stream
+    return p.qm_wt ? launch_size_q<W, H, true>(p, first, count, st)
+                   : launch_size_q<W, H, false>(p, first, count, st);
 }
 static cudaError_t launch_bucket(int tx_size, const KParams& p, int first, int count, cudaStream_t st) {
     switch (tx_size) {
@@ -152,6 +158,7 @@ extern "C" int svtgpu_plan_create(SvtGpuContext* c, const SvtGpuBlock* blocks, i
     uint32_t max_qrow = 0;
     for (int i = 0; i < n; ++i) max_qrow = dev[i].qrow > max_qrow ? dev[i].qrow : max_qrow;
     pl->max_qrow = max_qrow;
+    for (int i = 0; i < n; ++i) pl->uses_qm |= (dev[i].meta & META_USE_QM) != 0;
     if (n > 0) {
         if (cudaMalloc(&pl->d_blocks, size_t(n) * sizeof(DevBlock)) != cudaSuccess) { delete pl; CK(cudaGetLastError()); return SVTGPU_ERR_NOMEM; }
         CK(cudaMemcpyAsync(pl->d_blocks, dev.data(), size_t(n) * sizeof(DevBlock), cudaMemcpyHostToDevice, c->stream));
@@ -197,7 +204,8 @@ int svtgpu_run_internal(SvtGpuContext* c, const SvtGpuPlan* pl, const SvtGpuBuff
     p.residual = b->residual; p.pred = b->pred; p.recon = b->recon;
     p.coeff_in = b->coeff_in; p.coeff_out = b->coeff; p.qcoeff = b->qcoeff; p.dqcoeff = b->dqcoeff;
     p.eob = b->eob; p.energy = b->energy;
-    p.qtables = c->d_qtables; p.iscan = c->d_iscan; p.qm_wt = c->d_qm_wt; p.qm_iwt = c->d_qm_iwt;
+    p.qtables = c->d_qtables; p.iscan = c->d_iscan;
+    p.qm_wt = pl->uses_qm ? c->d_qm_wt : nullptr; p.qm_iwt = pl->uses_qm ? c->d_qm_iwt : nullptr;
     memcpy(p.iscan_off, c->iscan_off, sizeof(p.iscan_off));
     memcpy(p.qm_off, c->qm_off, sizeof(p.qm_off));
 

@@ -22,9 +22,12 @@ static void run_size(const KParams& p, int first, int count) {
         if (p.stages & STAGE_INV) stage_pred<W, H>(p, d, stage, 0, 1);
         int eob = 0;
         unsigned long long energy = 0;
+        QRow q = {};
+        if (p.stages & STAGE_QUANT) q = load_qrow<G::LOG_SCALE>(p.qtables + size_t(d.qrow) * 40);
         for (int r = 0; r < H; ++r) {
             int e; unsigned long long en;
-            phase_row<W, H>(p, d, r, buf.data(), block_iscan<W, H>(d, isc.data()), e, en);
+            if (p.qm_wt) phase_row<W, H, true>(p, d, q, r, buf.data(), block_iscan<W, H>(d, isc.data()), e, en);
+            else phase_row<W, H, false>(p, d, q, r, buf.data(), block_iscan<W, H>(d, isc.data()), e, en);
             eob = e > eob ? e : eob;
             energy += en;
         }
