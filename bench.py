@@ -24,6 +24,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
+from cidana_svt_av1_b200 import sharding  # noqa: E402
 from cidana_svt_av1_b200 import workloads as wl  # noqa: E402
 
 METRIC = "fwd-txfm+quant+inv-recon throughput"
@@ -48,10 +49,10 @@ def peaks():
     return 6650.0, "fallback"
 
 
-def make_batch(name, rank):
+def make_batch(name, rank, world=1):
+    """Rank `rank`'s shard of the weak-scaling job: world x n_frames frames, frame-major slices."""
     kw = dict(WORKLOADS[name][0])
-    kw["seed"] = kw["seed"] + 1000 * rank
-    return wl.make_frame_batch(**kw)
+    return sharding.rank_batch(wl.make_frame_batch, kw, kw["n_frames"], rank, world)
 
 
 class ClockSampler(threading.Thread):
@@ -156,7 +157,7 @@ def gpu_arm(args, rank, world, local_rank):
     torch.cuda.set_device(dev)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    batch = make_batch(args.workload, rank)
+    batch = make_batch(args.workload, rank, world)
     tables = load_tables(batch.bd)
     qm = load_qm() if "qm" in args.workload else None
     g = pkg.SvtGpu(local_rank)
@@ -210,15 +211,8 @@ def gpu_arm(args, rank, world, local_rank):
             step()
         st.synchronize()
     clocks = sampler.finish() if sampler else None
-    t_ms = torch.tensor([ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
-    ms = float(t_ms.item())
-    samples = torch.tensor([batch.n_samples], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(samples, op=dist.ReduceOp.SUM)
-    total_samples = float(samples.item())
-    value = total_samples * args.steps / (ms * 1e-3) / 1e6
+    ms, total_samples = sharding.reduce_step(ms, batch.n_samples, world, dev)
+    value = sharding.throughput_mcoeff(total_samples, args.steps, ms)
 
     if args.kernel_only:
         if rank == 0:

@@ -2,6 +2,7 @@
 // bucketing.  Header-only so the CPU-only tests can exercise it (tests/host_emul.cpp).
 #pragma once
 #include <stdint.h>
+#include <algorithm>
 #include <vector>
 #include "../../include/svt_gpu.h"
 #include "residual_kernel.cuh"
@@ -69,28 +70,45 @@ inline void build_iscan_tables(std::vector<int16_t>& all, int off[19][3]) {
         }
 }
 
-// Validates the caller's list and buckets it by (tx_size, tx_type); stable inside a bucket so that
-// spatially adjacent blocks stay adjacent.  Returns 0 or the 1-based index of the first bad block.
+// Validates the caller's list and buckets it by tx_size.  Inside a size bucket the caller's order is
+// kept in windows of kSortWindow blocks, and each window is stable-sorted by tx_type: warps then
+// mostly see one type (no divergence between 1-D kinds), while blocks that are neighbours in the
+// frame -- and share 32-byte DRAM sectors of the pixel rows -- are still processed within a few
+// CTAs of each other, so the second half of a sector is an L2 hit, not another DRAM read.
+// Returns 0 or the 1-based index of the first bad block.
+constexpr int kSortWindow = 4096;
 inline int bucket_blocks(const SvtGpuBlock* in, int n, std::vector<DevBlock>& out, int first[19],
                          int count[19]) {
-    int hist[19][16] = {};
+    int hist[19] = {};
     for (int i = 0; i < n; ++i) {
         const SvtGpuBlock& b = in[i];
         if (!tx_pair_valid(b.tx_size, b.tx_type)) return i + 1;
         if (b.bit_depth != 8 && b.bit_depth != 10) return i + 1;
         if (b.coeff_off & 3) return i + 1;
         if (b.plane > 2) return i + 1;
-        ++hist[b.tx_size][b.tx_type];
+        ++hist[b.tx_size];
     }
-    int start[19][16];
-    int acc = 0;
+    int acc = 0, fill[19];
     for (int s = 0; s < 19; ++s) {
-        first[s] = acc;
-        for (int t = 0; t < 16; ++t) { start[s][t] = acc; acc += hist[s][t]; }
-        count[s] = acc - first[s];
+        first[s] = fill[s] = acc;
+        count[s] = hist[s];
+        acc += hist[s];
     }
+    std::vector<int> order(n);  // caller indices, grouped by size, caller order inside a size
+    for (int i = 0; i < n; ++i) order[fill[in[i].tx_size]++] = i;
+    std::vector<int> win(kSortWindow);
+    for (int s = 0; s < 19; ++s)
+        for (int w0 = first[s]; w0 < first[s] + count[s]; w0 += kSortWindow) {
+            const int wn = std::min(kSortWindow, first[s] + count[s] - w0);
+            int th[17] = {};
+            for (int k = 0; k < wn; ++k) ++th[in[order[w0 + k]].tx_type + 1];
+            for (int t = 0; t < 16; ++t) th[t + 1] += th[t];
+            for (int k = 0; k < wn; ++k) win[th[in[order[w0 + k]].tx_type]++] = order[w0 + k];
+            std::copy(win.begin(), win.begin() + wn, order.begin() + w0);
+        }
     out.resize(n);
-    for (int i = 0; i < n; ++i) {
+    for (int k = 0; k < n; ++k) {
+        const int i = order[k];
         const SvtGpuBlock& b = in[i];
         DevBlock d;
         d.res_off = b.res_off; d.res_stride = b.res_stride;
@@ -100,7 +118,7 @@ inline int bucket_blocks(const SvtGpuBlock* in, int n, std::vector<DevBlock>& ou
                  (uint32_t(b.plane) << META_PLANE_SHIFT) |
                  ((b.flags & SVTGPU_BLK_CLAMP16) ? META_CLAMP16 : 0u) |
                  ((b.flags & SVTGPU_BLK_USE_QM) ? META_USE_QM : 0u);
-        out[start[b.tx_size][b.tx_type]++] = d;
+        out[k] = d;
     }
     return 0;
 }

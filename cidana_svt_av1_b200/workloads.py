@@ -135,24 +135,16 @@ def _layouts():
     return L
 
 
-def make_frame_batch(width, height, n_frames, bd, seed, qindex=120, laplace_b=6.0, use_qm=False,
-                     uniform=False, name=None):
-    """Mixed-size frame batch: every 64x64 superblock draws one of six luma partitions; both
-    chroma planes (4:2:0) use the half-size counterpart.  Residual/pred/recon are frame planes
-    (Y, U, V per frame, back to back) with their natural strides; coefficients are packed block
-    after block.  qrow = plane * 256 + qindex."""
-    rng = np.random.default_rng(seed)
-    pw = (width + 63) // 64 * 64
-    ph = (height + 63) // 64 * 64
+def _one_frame(rng, pw, ph, bd, qindex, laplace_b, use_qm, uniform):
+    """Blocks (offsets relative to the frame), residual and prediction planes of one frame."""
     sbx, sby = pw // 64, ph // 64
-    n_sb = sbx * sby * n_frames
+    n_sb = sbx * sby
     lay = _layouts()
     probs = np.array([l[0] for l in lay])
     choice = rng.choice(len(lay), size=n_sb, p=probs / probs.sum())
     sb_idx = np.arange(n_sb)
-    frame = sb_idx // (sbx * sby)
     sb_x = (sb_idx % sbx) * 64
-    sb_y = ((sb_idx // sbx) % sby) * 64
+    sb_y = (sb_idx // sbx) * 64
     y_size = pw * ph
     c_w, c_h = pw // 2, ph // 2
     c_size = c_w * c_h
@@ -165,23 +157,19 @@ def make_frame_batch(width, height, n_frames, bd, seed, qindex=120, laplace_b=6.
         for (w, h, pos) in groups:
             px = np.array([p[0] for p in pos])
             py = np.array([p[1] for p in pos])
-            k = len(pos)
             for plane in range(3):
                 if plane == 0:
-                    bw, bh, stride = w, h, pw
+                    bw, bh, stride, base = w, h, pw, 0
                     x = (sb_x[sel][:, None] + px[None, :]).ravel()
                     y = (sb_y[sel][:, None] + py[None, :]).ravel()
-                    base = frame[sel].repeat(k) * frame_size
                 else:
-                    bw, bh, stride = w // 2, h // 2, c_w
+                    bw, bh, stride, base = w // 2, h // 2, c_w, y_size + (plane - 1) * c_size
                     x = (sb_x[sel][:, None] // 2 + px[None, :] // 2).ravel()
                     y = (sb_y[sel][:, None] // 2 + py[None, :] // 2).ravel()
-                    base = frame[sel].repeat(k) * frame_size + y_size + (plane - 1) * c_size
                 b = np.zeros(len(x), BLOCK_DTYPE)
                 b["tx_size"] = TX_ID[(bw, bh)]
                 b["plane"] = plane
                 b["res_off"] = base + y * stride + x
-                b["rec_off"] = b["res_off"]
                 b["res_stride"] = stride
                 b["rec_stride"] = stride
                 parts.append(b)
@@ -202,12 +190,36 @@ def make_frame_batch(width, height, n_frames, bd, seed, qindex=120, laplace_b=6.
     blocks["qrow"] = blocks["plane"].astype(np.uint32) * 256 + qindex
     if use_qm:  # 2-D transform types only (EbFullLoop.c:532-539)
         blocks["flags"] = np.where(t < 9, BLK_USE_QM, 0)
-    total = frame_size * n_frames
     mval = (1 << bd) - 1
     if uniform:
-        residual = rng.integers(-mval, mval + 1, total).astype(np.int16)
+        residual = rng.integers(-mval, mval + 1, frame_size).astype(np.int16)
     else:
-        residual = np.clip(np.rint(rng.laplace(0.0, laplace_b, total)), -mval, mval).astype(np.int16)
-    pred = rng.integers(0, mval + 1, total).astype(np.uint8 if bd == 8 else np.uint16)
-    return _finish(blocks, residual, pred, bd,
+        residual = np.clip(np.rint(rng.laplace(0.0, laplace_b, frame_size)), -mval, mval).astype(np.int16)
+    pred = rng.integers(0, mval + 1, frame_size).astype(np.uint8 if bd == 8 else np.uint16)
+    return blocks, residual, pred
+
+
+def make_frame_batch(width, height, n_frames, bd, seed, qindex=120, laplace_b=6.0, use_qm=False,
+                     uniform=False, name=None, first_frame=0):
+    """Mixed-size frame batch: every 64x64 superblock draws one of six luma partitions; both
+    chroma planes (4:2:0) use the half-size counterpart.  Residual/pred/recon are frame planes
+    (Y, U, V per frame, back to back) with their natural strides; coefficients are packed block
+    after block.  qrow = plane * 256 + qindex.
+
+    Frame g of the job (g = first_frame .. first_frame + n_frames - 1) is a pure function of
+    (seed, g), so the shards the ranks of a multi-GPU run build are slices of one global job
+    (see sharding.frame_slice)."""
+    pw = (width + 63) // 64 * 64
+    ph = (height + 63) // 64 * 64
+    frame_size = pw * ph * 3 // 2
+    blocks, residual, pred = [], [], []
+    for k in range(n_frames):
+        rng = np.random.default_rng([seed, first_frame + k])
+        b, r, p = _one_frame(rng, pw, ph, bd, qindex, laplace_b, use_qm, uniform)
+        b["res_off"] += k * frame_size
+        b["rec_off"] = b["res_off"]
+        blocks.append(b)
+        residual.append(r)
+        pred.append(p)
+    return _finish(np.concatenate(blocks), np.concatenate(residual), np.concatenate(pred), bd,
                    name or f"{width}x{height}x{n_frames}f_bd{bd}{'_qm' if use_qm else ''}")
