@@ -253,23 +253,16 @@ def gpu_arm(args, rank, world, local_rank):
         except Exception:
             pass
 
-    # ---- e2e: host buffers in, host buffers out, copies and descriptor upload in the timed region -
-    with torch.cuda.stream(st):
-        h_out = {k: torch.empty(v.shape, dtype=v.dtype).pin_memory() for k, v in d.items()
-                 if k in ("recon", "qcoeff", "dqcoeff", "eob", "energy")}
-    h2d = h_res.numel() * 2 + h_pred.numel() * h_pred.element_size() + batch.n_blocks * 32
-    d2h = sum(v.numel() * v.element_size() for v in h_out.values())
+    # ---- e2e: host buffers in, host buffers out, through the public host-pipeline call -----------
+    # Every step: descriptor sort + upload, H2D of residual and prediction from page-locked memory,
+    # the kernels, D2H of qcoeff, dqcoeff, eob, energy and recon into page-locked memory; pictures
+    # of the batch are pipelined over the library's lanes (svtgpu_submit_host / svtgpu_wait_host).
+    hb = g.host_buffers(batch, pinned=True)
+    h2d = batch.residual.nbytes + batch.pred.nbytes + batch.n_blocks * 32
+    d2h = sum(v.nbytes for v in hb.out.values() if v is not None)
 
     def e2e_step():
-        p = g.plan(batch.blocks)  # validate + bucket + upload the descriptors
-        with torch.cuda.stream(st):
-            d["residual"].copy_(h_res, non_blocking=True)
-            d["pred"].copy_(h_pred, non_blocking=True)
-            g.run(p, pkg.api.STAGE_ALL, st.cuda_stream, **d)
-            for k, v in h_out.items():
-                v.copy_(d[k], non_blocking=True)
-        st.synchronize()
-        p.close()
+        g.run_host(batch, bufs=hb)
 
     e2e_steps = max(2, min(args.steps, 5))
     e2e_step()

@@ -28,6 +28,14 @@ class _Buffers(ctypes.Structure):  # SvtGpuBuffers
                                                "qcoeff", "dqcoeff", "eob", "energy")]
 
 
+class _HostFrame(ctypes.Structure):  # SvtGpuHostFrame
+    _fields_ = [("blocks", ctypes.c_void_p), ("n_blocks", ctypes.c_int), ("bit_depth", ctypes.c_int),
+                ("residual", ctypes.c_void_p), ("residual_elems", ctypes.c_size_t),
+                ("pred", ctypes.c_void_p), ("recon", ctypes.c_void_p), ("pixel_elems", ctypes.c_size_t),
+                ("qcoeff", ctypes.c_void_p), ("dqcoeff", ctypes.c_void_p), ("coeff_elems", ctypes.c_size_t),
+                ("eob", ctypes.c_void_p), ("energy", ctypes.c_void_p)]
+
+
 _lib = None
 
 
@@ -52,6 +60,8 @@ def load_library():
         L.svtgpu_upload_quant_tables.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
         L.svtgpu_upload_qmatrix.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
                                             ctypes.c_int, ctypes.c_void_p]
+        L.svtgpu_submit_host.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
+        L.svtgpu_wait_host.argtypes = [ctypes.c_void_p, ctypes.c_int]
         _lib = L
     return _lib
 
@@ -141,9 +151,43 @@ class SvtGpu:
         _check(lib().svtgpu_sync(self.handle), "svtgpu_sync")
 
     # ---- the end-to-end call: host buffers in, host buffers out -----------------------------------
-    def run_host(self, batch, stages=STAGE_ALL, want_coeff=False, coeff_in=None, plan=None):
-        """Uploads the batch (residual, prediction, block list), runs, downloads every output.
-        Returns a dict of numpy arrays like the oracle runners do."""
+    def host_buffers(self, batch, pinned=True):
+        """Output (and page-locked input) buffers a caller of the host pipeline owns: allocate
+        once, reuse for every run over batches of this geometry."""
+        return HostBuffers(batch, pinned)
+
+    def submit_host(self, frame, out, stages=STAGE_ALL, residual=None, pred=None):
+        """Queue one picture (a Batch whose offsets are relative to its own arrays) on the
+        pipeline; `out` is a dict of host arrays (qcoeff, dqcoeff, eob, energy, recon) sized for
+        this picture.  Returns the ticket.  Asynchronous: see svtgpu_submit_host."""
+        residual = frame.residual if residual is None else residual
+        pred = frame.pred if pred is None else pred
+        hf = _HostFrame(_P(frame.blocks).value, frame.n_blocks, int(frame.bd),
+                        _P(residual).value, residual.size, _P(pred).value, _P(out["recon"]).value,
+                        pred.size, _P(out["qcoeff"]).value, _P(out["dqcoeff"]).value, frame.n_coeff,
+                        _P(out["eob"]).value, _P(out["energy"]).value if out.get("energy") is not None else None)
+        t = ctypes.c_int(-1)
+        _check(lib().svtgpu_submit_host(self.handle, ctypes.byref(hf), int(stages), ctypes.byref(t)),
+               "svtgpu_submit_host")
+        return t.value
+
+    def wait_host(self, ticket=-1):
+        _check(lib().svtgpu_wait_host(self.handle, int(ticket)), "svtgpu_wait_host")
+
+    def run_host(self, batch, stages=STAGE_ALL, bufs=None):
+        """Host arrays in, host arrays out, every copy included: each picture of the batch goes
+        through svtgpu_submit_host (upload, kernels and download of consecutive pictures overlap),
+        then one wait.  Returns a dict of numpy arrays like the oracle runners do."""
+        bufs = bufs or HostBuffers(batch, pinned=False)
+        for k, fr in enumerate(batch.frames()):
+            self.submit_host(fr, bufs.frame_out(k), stages, *bufs.frame_in(k))
+        self.wait_host()
+        return bufs.out
+
+    def run_staged(self, batch, stages=STAGE_ALL, want_coeff=False, coeff_in=None, plan=None):
+        """Any stage combination through the batch API (svtgpu_plan_create + svtgpu_run) on
+        torch-allocated device buffers, synchronous: upload, run, download everything.  Used
+        where the stages are split (forward only, quantiser on given coefficients, ...)."""
         import torch
         dev = torch.device("cuda", self.device)
         own_plan = plan is None
@@ -174,6 +218,54 @@ class SvtGpu:
         if own_plan:
             plan.close()
         return out
+
+
+class HostBuffers:
+    """Host-side arrays of one batch geometry: outputs always, and page-locked copies of the
+    inputs when `pinned` (what a caller that wants full PCIe speed would hold)."""
+
+    def __init__(self, batch, pinned=True):
+        self.batch = batch
+        self.pinned = pinned
+        n, nc = batch.n_blocks, batch.n_coeff
+        pdt = batch.pred.dtype
+
+        def alloc(count, dtype):
+            if not pinned:
+                return np.zeros(count, dtype)
+            import torch
+            t = torch.zeros(max(count, 1) * np.dtype(dtype).itemsize, dtype=torch.uint8).pin_memory()
+            self._keep.append(t)
+            return t.numpy().view(dtype)[:count]
+
+        self._keep = []
+        self.out = dict(qcoeff=alloc(nc, np.int32), dqcoeff=alloc(nc, np.int32), eob=alloc(n, np.uint16),
+                        energy=alloc(n, np.uint64), recon=alloc(batch.pred.size, pdt), coeff=None)
+        if pinned:
+            self.residual = alloc(batch.residual.size, np.int16)
+            self.pred = alloc(batch.pred.size, pdt)
+            self.residual[:] = batch.residual
+            self.pred[:] = batch.pred
+        else:
+            self.residual, self.pred = batch.residual, batch.pred
+        self._frames = batch.frames()
+
+    def frame_in(self, k):
+        f = self._frames[k]
+        if len(self._frames) == 1 and f is self.batch:
+            return self.residual, self.pred
+        e0 = f.elem0
+        return self.residual[e0:e0 + f.residual.size], self.pred[e0:e0 + f.pred.size]
+
+    def frame_out(self, k):
+        f = self._frames[k]
+        if len(self._frames) == 1 and f is self.batch:
+            return self.out
+        o = self.out
+        b0, c0, e0 = f.block0, f.coeff0, f.elem0
+        return dict(qcoeff=o["qcoeff"][c0:c0 + f.n_coeff], dqcoeff=o["dqcoeff"][c0:c0 + f.n_coeff],
+                    eob=o["eob"][b0:b0 + f.n_blocks], energy=o["energy"][b0:b0 + f.n_blocks],
+                    recon=o["recon"][e0:e0 + f.pred.size])
 
 
 # ---- Level B mirrors: the reference's entry points on host numpy arrays ----------------------------

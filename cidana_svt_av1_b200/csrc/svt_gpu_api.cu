@@ -93,6 +93,7 @@ extern "C" int svtgpu_create(SvtGpuContext** out, int device) {
 extern "C" void svtgpu_destroy(SvtGpuContext* c) {
     if (!c) return;
     cudaSetDevice(c->device);
+    svtgpu_host_release(c);
     cudaStreamSynchronize(c->stream);
     for (int i = 0; i < SvtGpuContext::kSide; ++i) {
         cudaStreamSynchronize(c->side[i]);

@@ -1,0 +1,174 @@
+// Host-buffer pipeline: svtgpu_submit_host / svtgpu_wait_host (include/svt_gpu.h).
+// A ring of kHostSlots lanes, each with its own stream and device buffers.  A submission does
+//   sort descriptors (host) -> H2D descriptors, residual, prediction -> kernels -> D2H outputs
+// on its lane's stream; lanes overlap each other, so in steady state the two copy engines and
+// the SMs are all busy.  Nothing here computes on the host: a CUDA failure is returned, never
+// worked around.
+#include <stdio.h>
+#include <string.h>
+#include <new>
+#include <vector>
+#include "host_plan.h"
+#include "svt_gpu_internal.h"
+
+using namespace svt;
+
+namespace {
+
+template <class T>
+int grow(T*& p, size_t& cap, size_t need, cudaStream_t st) {
+    if (need <= cap) return SVTGPU_OK;
+    CK(cudaStreamSynchronize(st));
+    if (p) CK(cudaFree(p));
+    p = nullptr;
+    cap = 0;
+    const size_t want = need + need / 4;
+    if (cudaMalloc(reinterpret_cast<void**>(&p), want * sizeof(T)) != cudaSuccess) {
+        cudaGetLastError();
+        svtgpu_set_error("%s%s (line %d)", "out of device memory in the host pipeline", "", __LINE__);
+        return SVTGPU_ERR_NOMEM;
+    }
+    cap = want;
+    return SVTGPU_OK;
+}
+
+int slot_init(HostSlot& s) {
+    if (s.st) return SVTGPU_OK;
+    CK(cudaStreamCreateWithFlags(&s.st, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+    return SVTGPU_OK;
+}
+
+int slot_wait(HostSlot& s) {
+    if (s.busy) {
+        CK(cudaEventSynchronize(s.done));
+        s.busy = false;
+    }
+    return SVTGPU_OK;
+}
+
+}  // namespace
+
+#define TRY(x)                        \
+    do {                              \
+        const int rc_ = (x);          \
+        if (rc_ != SVTGPU_OK) return rc_; \
+    } while (0)
+
+extern "C" int svtgpu_submit_host(SvtGpuContext* c, const SvtGpuHostFrame* f, int stages, int* ticket) {
+    if (!c || !f || f->n_blocks < 0 || (f->n_blocks && !f->blocks)) return SVTGPU_ERR_ARG;
+    if (!(stages & SVTGPU_STAGE_ALL) || (stages & ~SVTGPU_STAGE_ALL)) return SVTGPU_ERR_ARG;
+    if (f->bit_depth != 8 && f->bit_depth != 10) return SVTGPU_ERR_ARG;
+    const bool fwd = stages & STAGE_FWD, qnt = stages & STAGE_QUANT, inv = stages & STAGE_INV;
+    if (!fwd || !qnt) return SVTGPU_ERR_ARG;  // the pipeline carries the fused path (optionally without INV)
+    if (!f->residual || !f->qcoeff || !f->dqcoeff || !f->eob) return SVTGPU_ERR_ARG;
+    if (inv && (!f->pred || !f->recon)) return SVTGPU_ERR_ARG;
+    CK(cudaSetDevice(c->device));
+    HostSlot& s = c->host[c->host_next];
+    c->host_next = (c->host_next + 1) % SvtGpuContext::kHostSlots;
+    TRY(slot_init(s));
+    TRY(slot_wait(s));
+    const int n = f->n_blocks;
+    const int my_ticket = c->host_tickets++;
+    s.ticket = my_ticket;
+    if (ticket) *ticket = my_ticket;
+    if (n == 0) return SVTGPU_OK;
+
+    // descriptors: validate + bucket on the host, straight into page-locked staging
+    SvtGpuPlan plan;
+    plan.ctx = c;
+    plan.n = n;
+    if (size_t(n) > s.cap_blocks) {
+        CK(cudaStreamSynchronize(s.st));
+        if (s.h_blocks) CK(cudaFreeHost(s.h_blocks));
+        s.h_blocks = nullptr;
+        CK(cudaMallocHost(reinterpret_cast<void**>(&s.h_blocks), (size_t(n) + n / 4) * sizeof(DevBlock)));
+    }
+    TRY(grow(s.d_blocks, s.cap_blocks, size_t(n), s.st));
+    static thread_local BucketScratch scratch;
+    const int bad = bucket_blocks(f->blocks, n, s.h_blocks, plan.first, plan.count, scratch);
+    if (bad) {
+        char idx[32];
+        snprintf(idx, sizeof(idx), "%d", bad - 1);
+        svtgpu_set_error("%s%s (line %d)", "invalid SvtGpuBlock at index ", idx, __LINE__);
+        return SVTGPU_ERR_ARG;
+    }
+    for (int i = 0; i < n; ++i) {
+        const SvtGpuBlock& b = f->blocks[i];
+        if (b.bit_depth != f->bit_depth) return SVTGPU_ERR_ARG;
+        plan.max_qrow = b.qrow > plan.max_qrow ? b.qrow : plan.max_qrow;
+        plan.uses_qm |= (b.flags & SVTGPU_BLK_USE_QM) != 0;
+    }
+    plan.d_blocks = s.d_blocks;
+
+    const size_t px = f->bit_depth == 8 ? 1 : 2;
+    TRY(grow(s.d_res, s.cap_res, f->residual_elems, s.st));
+    if (inv) {
+        char* pix = static_cast<char*>(s.d_pix);
+        TRY(grow(pix, s.cap_pix, f->pixel_elems * px, s.st));
+        s.d_pix = pix;
+    }
+    {
+        size_t cap2 = s.cap_coeff;
+        TRY(grow(s.d_q, s.cap_coeff, f->coeff_elems, s.st));
+        TRY(grow(s.d_dq, cap2, f->coeff_elems, s.st));
+        size_t cap_e = s.cap_n;
+        TRY(grow(s.d_eob, s.cap_n, size_t(n), s.st));
+        TRY(grow(s.d_energy, cap_e, size_t(n), s.st));
+    }
+
+    CK(cudaMemcpyAsync(s.d_blocks, s.h_blocks, size_t(n) * sizeof(DevBlock), cudaMemcpyHostToDevice, s.st));
+    CK(cudaMemcpyAsync(s.d_res, f->residual, f->residual_elems * sizeof(int16_t), cudaMemcpyHostToDevice, s.st));
+    if (inv) CK(cudaMemcpyAsync(s.d_pix, f->pred, f->pixel_elems * px, cudaMemcpyHostToDevice, s.st));
+
+    SvtGpuBuffers b;
+    memset(&b, 0, sizeof(b));
+    b.residual = s.d_res;
+    b.pred = s.d_pix;
+    b.recon = s.d_pix;  // in place, like the reference
+    b.qcoeff = s.d_q;
+    b.dqcoeff = s.d_dq;
+    b.eob = s.d_eob;
+    b.energy = s.d_energy;
+    TRY(svtgpu_run_internal(c, &plan, &b, stages, s.st));
+
+    CK(cudaMemcpyAsync(f->qcoeff, s.d_q, f->coeff_elems * sizeof(int32_t), cudaMemcpyDeviceToHost, s.st));
+    CK(cudaMemcpyAsync(f->dqcoeff, s.d_dq, f->coeff_elems * sizeof(int32_t), cudaMemcpyDeviceToHost, s.st));
+    CK(cudaMemcpyAsync(f->eob, s.d_eob, size_t(n) * sizeof(uint16_t), cudaMemcpyDeviceToHost, s.st));
+    if (f->energy)
+        CK(cudaMemcpyAsync(f->energy, s.d_energy, size_t(n) * sizeof(uint64_t), cudaMemcpyDeviceToHost, s.st));
+    if (inv) CK(cudaMemcpyAsync(f->recon, s.d_pix, f->pixel_elems * px, cudaMemcpyDeviceToHost, s.st));
+    CK(cudaEventRecord(s.done, s.st));
+    s.busy = true;
+    return SVTGPU_OK;
+}
+
+extern "C" int svtgpu_wait_host(SvtGpuContext* c, int ticket) {
+    if (!c) return SVTGPU_ERR_ARG;
+    CK(cudaSetDevice(c->device));
+    for (int i = 0; i < SvtGpuContext::kHostSlots; ++i) {
+        HostSlot& s = c->host[i];
+        if (ticket < 0 || s.ticket == ticket) TRY(slot_wait(s));
+    }
+    return SVTGPU_OK;
+}
+
+// called by svtgpu_destroy
+void svtgpu_host_release(SvtGpuContext* c) {
+    for (int i = 0; i < SvtGpuContext::kHostSlots; ++i) {
+        HostSlot& s = c->host[i];
+        if (!s.st) continue;
+        cudaStreamSynchronize(s.st);
+        cudaFree(s.d_blocks);
+        cudaFreeHost(s.h_blocks);
+        cudaFree(s.d_res);
+        cudaFree(s.d_pix);
+        cudaFree(s.d_q);
+        cudaFree(s.d_dq);
+        cudaFree(s.d_eob);
+        cudaFree(s.d_energy);
+        cudaEventDestroy(s.done);
+        cudaStreamDestroy(s.st);
+        s = HostSlot();
+    }
+}

@@ -17,8 +17,34 @@ void svtgpu_set_error(const char* fmt, const char* a, const char* b, int line);
         }                                                                                     \
     } while (0)
 
+// One lane of the host-buffer pipeline (svtgpu_submit_host): a stream, device buffers grown on
+// demand and page-locked staging for the sorted block descriptors.
+struct HostSlot {
+    cudaStream_t st = nullptr;
+    cudaEvent_t done = nullptr;
+    bool busy = false;
+    int ticket = -1;
+    svt::DevBlock* d_blocks = nullptr;
+    svt::DevBlock* h_blocks = nullptr;  // page-locked
+    size_t cap_blocks = 0;
+    int16_t* d_res = nullptr;
+    size_t cap_res = 0;
+    void* d_pix = nullptr;  // prediction in, reconstruction out (in place)
+    size_t cap_pix = 0;     // bytes
+    int32_t* d_q = nullptr;
+    int32_t* d_dq = nullptr;
+    size_t cap_coeff = 0;
+    uint16_t* d_eob = nullptr;
+    uint64_t* d_energy = nullptr;
+    size_t cap_n = 0;
+};
+
 struct SvtGpuContext {
     static constexpr int kSide = 4;
+    static constexpr int kHostSlots = 3;
+    HostSlot host[kHostSlots];
+    int host_next = 0;
+    int host_tickets = 0;
     int device = 0;
     cudaStream_t stream = nullptr;
     cudaStream_t side[kSide] = {};
@@ -47,3 +73,6 @@ struct SvtGpuPlan {
 // svtgpu_run plus the internal STAGE_FWD_FULL flag (used by the RTCD-level forward slots)
 int svtgpu_run_internal(SvtGpuContext* c, const SvtGpuPlan* pl, const SvtGpuBuffers* b, int stages,
                         void* cuda_stream);
+
+// frees the lanes of the host-buffer pipeline (svt_gpu_host.cu)
+void svtgpu_host_release(SvtGpuContext* c);

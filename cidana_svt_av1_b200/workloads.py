@@ -55,6 +55,8 @@ class Batch:
         self.n_coeff = int(n_coeff)
         self.bd = bd
         self.name = name
+        self.frame_bounds = None  # [(block0, block1, elem0, elem1)] when the batch is made of frames
+        self._frames = None
 
     @property
     def n_blocks(self):
@@ -63,6 +65,28 @@ class Batch:
     @property
     def n_samples(self):
         return int(AREA[self.blocks["tx_size"]].sum())
+
+    def frames(self):
+        """The batch as independent pictures: one Batch per frame whose arrays are views into this
+        batch's arrays and whose block offsets are relative to the frame (what a per-picture
+        caller holds).  A batch without frame structure is a single picture."""
+        if self._frames is None:
+            if not self.frame_bounds:
+                self._frames = [self]
+            else:
+                out = []
+                for (b0, b1, e0, e1) in self.frame_bounds:
+                    blk = self.blocks[b0:b1].copy()
+                    c0 = int(blk["coeff_off"][0]) if len(blk) else 0
+                    blk["res_off"] -= e0
+                    blk["rec_off"] -= e0
+                    blk["coeff_off"] -= c0
+                    f = Batch(blk, self.residual[e0:e1], self.pred[e0:e1],
+                              int(CODED[blk["tx_size"]].sum()), self.bd, f"{self.name}[{len(out)}]")
+                    f.block0, f.coeff0, f.elem0 = b0, c0, e0
+                    out.append(f)
+                self._frames = out
+        return self._frames
 
     def algorithmic_bytes(self):
         """residual 2 B + prediction + q/dq 8 B on the coded part + recon, plus
@@ -221,5 +245,9 @@ def make_frame_batch(width, height, n_frames, bd, seed, qindex=120, laplace_b=6.
         blocks.append(b)
         residual.append(r)
         pred.append(p)
-    return _finish(np.concatenate(blocks), np.concatenate(residual), np.concatenate(pred), bd,
-                   name or f"{width}x{height}x{n_frames}f_bd{bd}{'_qm' if use_qm else ''}")
+    batch = _finish(np.concatenate(blocks), np.concatenate(residual), np.concatenate(pred), bd,
+                    name or f"{width}x{height}x{n_frames}f_bd{bd}{'_qm' if use_qm else ''}")
+    ends = np.cumsum([len(b) for b in blocks])
+    batch.frame_bounds = [(int(e - len(b)), int(e), k * frame_size, (k + 1) * frame_size)
+                          for k, (b, e) in enumerate(zip(blocks, ends))]
+    return batch

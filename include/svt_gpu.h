@@ -103,6 +103,36 @@ int svtgpu_memcpy_h2d(SvtGpuContext *ctx, void *dev, const void *host, size_t by
 int svtgpu_memcpy_d2h(SvtGpuContext *ctx, void *host, const void *dev, size_t bytes);
 int svtgpu_memset(SvtGpuContext *ctx, void *dev, int value, size_t bytes);
 
+/* ---- host-buffer pipeline: the end-to-end call ------------------------------------------------
+ * One picture (or any independent group of blocks) whose inputs and outputs live in HOST memory.
+ * svtgpu_submit_host copies the inputs to the device, runs the stages and copies every output
+ * back, all asynchronously on one of a small ring of internal streams, so that the upload of
+ * picture i+1, the kernels of picture i and the download of picture i-1 overlap (separate copy
+ * engines per direction).  The caller's buffers must stay valid and untouched until
+ * svtgpu_wait_host returns; they should be page-locked (svtgpu_malloc_host) -- pageable memory
+ * works but serialises the copies.  Offsets in `blocks` are relative to the pointers given here.
+ * This is the batched counterpart of calling av1_estimate_transform + av1_quantize_inv_quantize +
+ * av1_inv_transform_recon for every block of the picture (EbCodingLoop.c:655-731). */
+typedef struct SvtGpuHostFrame {
+    const SvtGpuBlock *blocks;
+    int n_blocks;
+    int bit_depth;           /* 8: pixels are uint8; 10: uint16 */
+    const int16_t *residual; /* residual_elems int16 */
+    size_t residual_elems;
+    const void *pred;        /* pixel_elems pixels */
+    void *recon;             /* pixel_elems pixels out (may equal pred) */
+    size_t pixel_elems;
+    int32_t *qcoeff;         /* coeff_elems int32 out */
+    int32_t *dqcoeff;        /* coeff_elems int32 out */
+    size_t coeff_elems;
+    uint16_t *eob;           /* n_blocks out */
+    uint64_t *energy;        /* n_blocks out, or NULL */
+} SvtGpuHostFrame;
+/* returns immediately after queueing; *ticket (optional) identifies the submission */
+int svtgpu_submit_host(SvtGpuContext *ctx, const SvtGpuHostFrame *frame, int stages, int *ticket);
+/* blocks until submission `ticket` (or all of them when ticket < 0) has fully landed in host memory */
+int svtgpu_wait_host(SvtGpuContext *ctx, int ticket);
+
 /* scan tables the library generates (av1_scan_orders, EbTransforms.h:3349): for tests */
 int svtgpu_get_iscan(int tx_size, int scan_class, int16_t *iscan_out /* max_eob entries */);
 

@@ -34,7 +34,10 @@ def tables(bd):
 
 
 def run_gpu(batch, stages=7, qm=None, coeff_in=None, want_coeff=False):
-    return ctx(batch.bd, qm).run_host(batch, stages=stages, coeff_in=coeff_in, want_coeff=want_coeff)
+    g = ctx(batch.bd, qm)
+    if coeff_in is None and not want_coeff and stages == 7:
+        return g.run_host(batch)  # the host pipeline (svtgpu_submit_host / svtgpu_wait_host)
+    return g.run_staged(batch, stages=stages, coeff_in=coeff_in, want_coeff=want_coeff)
 
 
 def check(a, b, what):
@@ -123,6 +126,45 @@ def test_frame_batches_vs_oracle():
     qm = qm_pack(load_qmatrices(), 6)
     bq = wl.make_frame_batch(512, 256, 1, 10, seed=20241, qindex=100, laplace_b=24.0, use_qm=True)
     check(run_gpu(bq, qm=qm), run_oracle(bq, tables(10), load_scans(), qm=qm, threads=8), "frame_qm")
+
+
+def test_host_pipeline_many_frames_reused_buffers():
+    """svtgpu_submit_host / svtgpu_wait_host: more pictures than lanes, page-locked buffers reused
+    across runs, results land in the caller's arrays; and the path without reconstruction."""
+    g = ctx(8)
+    batch = wl.make_frame_batch(320, 192, 7, 8, seed=99)
+    assert len(batch.frames()) == 7
+    want = run_oracle(batch, tables(8), load_scans(), threads=8)
+    hb = g.host_buffers(batch, pinned=True)
+    for rep in range(3):
+        for v in hb.out.values():
+            if v is not None:
+                v[:] = 0x5A if v.dtype == np.uint8 else 12345
+        check(g.run_host(batch, bufs=hb), want, f"pipeline rep {rep}")
+    # pageable buffers, tickets waited one by one
+    hb2 = g.host_buffers(batch, pinned=False)
+    tickets = [g.submit_host(fr, hb2.frame_out(k), 7, *hb2.frame_in(k)) for k, fr in enumerate(batch.frames())]
+    assert tickets == sorted(tickets) and len(set(tickets)) == 7
+    for t in tickets:
+        g.wait_host(t)
+    g.wait_host()
+    check(hb2.out, want, "pipeline pageable")
+    # forward + quantiser only: reconstruction buffer untouched
+    hb3 = g.host_buffers(batch, pinned=False)
+    hb3.out["recon"][:] = 7
+    out = g.run_host(batch, stages=3, bufs=hb3)
+    for k in ("qcoeff", "dqcoeff", "eob", "energy"):
+        assert np.array_equal(out[k], want[k]), k
+    assert (out["recon"] == 7).all()
+    # a bad block is refused, not worked around
+    bad = batch.frames()[0]
+    blk = bad.blocks.copy()
+    blk["tx_type"][0] = 15
+    blk["tx_size"][0] = 4  # 64x64 only allows DCT_DCT
+    bb = wl.Batch(blk, bad.residual, bad.pred, bad.n_coeff, 8, "bad")
+    with pytest.raises(pkg.api.SvtGpuError):
+        g.submit_host(bb, hb2.frame_out(0))
+    g.wait_host()
 
 
 # ---- levels A and B: the reference's own signatures, host pointers ---------------------------------
