@@ -225,22 +225,34 @@ def gpu_arm(args, rank, world, local_rank):
     sizes = batch.blocks["tx_size"]
     by_size = {int(s): int((wl.AREA[sizes[sizes == s]]).sum()) for s in np.unique(sizes)}
     dom = max(by_size, key=by_size.get)
-    sub_blocks = batch.blocks[sizes == dom]
-    sub = wl.Batch(sub_blocks, batch.residual, batch.pred, batch.n_coeff, batch.bd, "dominant")
-    plan_dom = g.plan(sub_blocks)
-    for _ in range(3):
-        g.run(plan_dom, pkg.api.STAGE_ALL, st.cuda_stream, **d)
-    reps = 20
-    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    st.synchronize()
-    k0.record(st)
-    for _ in range(reps):
-        g.run(plan_dom, pkg.api.STAGE_ALL, st.cuda_stream, **d)
-    k1.record(st)
-    st.synchronize()
-    k_ms = k0.elapsed_time(k1) / reps
-    k_bytes = sub.algorithmic_bytes()
+
+    def time_bucket(tx_size, reps=20):
+        """One size bucket alone on the launching stream: (ms per launch, algorithmic bytes)."""
+        sub_blocks = batch.blocks[sizes == tx_size]
+        sub = wl.Batch(sub_blocks, batch.residual, batch.pred, batch.n_coeff, batch.bd, "bucket")
+        pl = g.plan(sub_blocks)
+        for _ in range(3):
+            g.run(pl, pkg.api.STAGE_ALL, st.cuda_stream, **d)
+        k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        st.synchronize()
+        k0.record(st)
+        for _ in range(reps):
+            g.run(pl, pkg.api.STAGE_ALL, st.cuda_stream, **d)
+        k1.record(st)
+        st.synchronize()
+        pl.close()
+        return k0.elapsed_time(k1) / reps, sub.algorithmic_bytes()
+
+    k_ms, k_bytes = time_bucket(dom)
     achieved = k_bytes / (k_ms * 1e-3) / 1e9
+    per_kernel = None
+    if args.per_kernel and rank == 0:
+        per_kernel = {}
+        for s_ in sorted(by_size, key=by_size.get, reverse=True):
+            t_, b_ = time_bucket(s_)
+            per_kernel[f"{wl.TX_W[s_]}x{wl.TX_H[s_]}"] = {"us": round(t_ * 1e3, 2), "GB/s": round(b_ / t_ / 1e6, 1),
+                                                        "frac": round(b_ / t_ / 1e6 / hbm, 3)}
+        print("per-kernel (each bucket alone):", json.dumps(per_kernel), file=sys.stderr, flush=True)
     roof = {"bound": "hbm", "kernel": f"residual_kernel<{wl.TX_W[dom]},{wl.TX_H[dom]}>",
             "achieved": achieved, "peak": hbm, "peak_source": which, "unit": "GB/s", "frac": achieved / hbm,
             "traffic": None, "launch_ms": k_ms, "algorithmic_bytes_per_launch": k_bytes,
@@ -305,6 +317,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="1080p8", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--per-kernel", action="store_true", help="time every size bucket alone (stderr)")
     ap.add_argument("--kernel-only", action="store_true",
                     help="timed steps only (for ncu): no roofline sub-run, e2e or cpu_baseline")
     args = ap.parse_args()

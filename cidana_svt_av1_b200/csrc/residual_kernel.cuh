@@ -204,48 +204,50 @@ SVT_HD void g2s_commit_wait() {
     asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;\n" ::: "memory");
 #endif
 }
-// one block: global (strided) -> shared (dense); threads tid, tid + nthr, ... of the copy team
-// `flip`: global row r lands in shared row rows-1-r (and comes back from it).  The up/down flip of
+// one block: global (strided) <-> shared (dense) by a copy team of NTHR threads.
+// `flip`: global row r lands in shared row ROWS-1-r (and comes back from it).  The up/down flip of
 // the FLIPADST types (EbTransforms.c:3739-3744, :8258-8264) is folded into the copies this way,
 // so the transform phases never branch on it.
-template <int CH>
-SVT_HD void stage_in_t(char* sdst, const char* gsrc, int rows, int row_bytes, size_t gstride,
-                       bool flip, int tid, int nthr) {
-    const int per_row = row_bytes / CH;
+// Fast path: base address and stride aligned to min(16, ROW_BYTES) -- every trip count and
+// index split is a compile-time constant.  Anything else (the encoder may pass any offset) goes
+// through one shared out-of-line loop with the widest chunk the addresses allow.
+SVT_NOINLINE void stage_slow(char* s, char* g, int rows, int row_bytes, size_t gstride, bool flip,
+                             int tid, int nthr, bool in) {
+    const int ch = align_chunk(size_t(g) | gstride, row_bytes);
+    const int per_row = row_bytes / ch;
     for (int i = tid; i < rows * per_row; i += nthr) {
         const int r = i / per_row, k = i - r * per_row;
-        const int sr = flip ? rows - 1 - r : r;
-        g2s_chunk<CH>(sdst + sr * row_bytes + k * CH, gsrc + size_t(r) * gstride + k * CH);
+        char* sp = s + (flip ? rows - 1 - r : r) * row_bytes + k * ch;
+        char* gp = g + size_t(r) * gstride + k * ch;
+        char* dst = in ? sp : gp;
+        const char* src = in ? gp : sp;
+        switch (ch) {
+        case 16: copy_chunk<16>(dst, src); break;
+        case 8: copy_chunk<8>(dst, src); break;
+        case 4: copy_chunk<4>(dst, src); break;
+        case 2: copy_chunk<2>(dst, src); break;
+        default: copy_chunk<1>(dst, src); break;
+        }
     }
 }
-template <int CH>
-SVT_HD void stage_out_t(char* gdst, const char* ssrc, int rows, int row_bytes, size_t gstride,
-                        bool flip, int tid, int nthr) {
-    const int per_row = row_bytes / CH;
-    for (int i = tid; i < rows * per_row; i += nthr) {
-        const int r = i / per_row, k = i - r * per_row;
-        const int sr = flip ? rows - 1 - r : r;
-        copy_chunk<CH>(gdst + size_t(r) * gstride + k * CH, ssrc + sr * row_bytes + k * CH);
+template <int ROWS, int ROW_BYTES, int NTHR, bool IN>
+SVT_HD void stage_copy(char* s, char* g, size_t gstride, bool flip, int tid) {
+    constexpr int CH = ROW_BYTES < 16 ? ROW_BYTES : 16;
+    if ((size_t(g) | gstride) & size_t(CH - 1)) {
+        stage_slow(s, g, ROWS, ROW_BYTES, gstride, flip, tid, NTHR, IN);
+        return;
     }
-}
-SVT_HD void stage_in(char* sdst, const char* gsrc, int rows, int row_bytes, size_t gstride, bool flip,
-                     int tid, int nthr) {
-    switch (align_chunk(size_t(gsrc) | gstride, row_bytes)) {
-    case 16: stage_in_t<16>(sdst, gsrc, rows, row_bytes, gstride, flip, tid, nthr); break;
-    case 8: stage_in_t<8>(sdst, gsrc, rows, row_bytes, gstride, flip, tid, nthr); break;
-    case 4: stage_in_t<4>(sdst, gsrc, rows, row_bytes, gstride, flip, tid, nthr); break;
-    case 2: stage_in_t<2>(sdst, gsrc, rows, row_bytes, gstride, flip, tid, nthr); break;
-    default: stage_in_t<1>(sdst, gsrc, rows, row_bytes, gstride, flip, tid, nthr); break;
-    }
-}
-SVT_HD void stage_out(char* gdst, const char* ssrc, int rows, int row_bytes, size_t gstride, bool flip,
-                      int tid, int nthr) {
-    switch (align_chunk(size_t(gdst) | gstride, row_bytes)) {
-    case 16: stage_out_t<16>(gdst, ssrc, rows, row_bytes, gstride, flip, tid, nthr); break;
-    case 8: stage_out_t<8>(gdst, ssrc, rows, row_bytes, gstride, flip, tid, nthr); break;
-    case 4: stage_out_t<4>(gdst, ssrc, rows, row_bytes, gstride, flip, tid, nthr); break;
-    case 2: stage_out_t<2>(gdst, ssrc, rows, row_bytes, gstride, flip, tid, nthr); break;
-    default: stage_out_t<1>(gdst, ssrc, rows, row_bytes, gstride, flip, tid, nthr); break;
+    constexpr int PER_ROW = ROW_BYTES / CH, TOTAL = ROWS * PER_ROW, ITERS = (TOTAL + NTHR - 1) / NTHR;
+#pragma unroll
+    for (int it = 0; it < ITERS; ++it) {
+        const int i = tid + it * NTHR;
+        if (TOTAL % NTHR == 0 || i < TOTAL) {
+            const int r = i / PER_ROW, k = i % PER_ROW;
+            char* sp = s + (flip ? ROWS - 1 - r : r) * ROW_BYTES + k * CH;
+            char* gp = g + size_t(r) * gstride + k * CH;
+            if constexpr (IN) g2s_chunk<CH>(sp, gp);
+            else copy_chunk<CH>(gp, sp);
+        }
     }
 }
 
@@ -542,22 +544,29 @@ SVT_HD void phase_inv_col(const DevBlock& d, int c, const int* buf, void* pix) {
 // ---- per-block staging steps shared by the kernel and the host emulation ---------------------------
 SVT_HD int px_bytes(const DevBlock& d) { return (d.meta & META_BD10) ? 2 : 1; }
 SVT_HD bool ud_flip(const DevBlock& d) { return vtx_of(d.meta & META_TYPE_MASK) == 2; }
-template <int W, int H>
-SVT_HD void stage_residual(const KParams& p, const DevBlock& d, int16_t* sres, int tid, int nthr) {
-    stage_in(reinterpret_cast<char*>(sres), reinterpret_cast<const char*>(p.residual + d.res_off), H,
-             W * 2, size_t(d.res_stride) * 2, ud_flip(d), tid, nthr);
+template <int W, int H, int NTHR>
+SVT_HD void stage_residual(const KParams& p, const DevBlock& d, int16_t* sres, int tid) {
+    stage_copy<H, W * 2, NTHR, true>(reinterpret_cast<char*>(sres),
+                                     reinterpret_cast<char*>(const_cast<int16_t*>(p.residual + d.res_off)),
+                                     size_t(d.res_stride) * 2, ud_flip(d), tid);
 }
-template <int W, int H>
-SVT_HD void stage_pred(const KParams& p, const DevBlock& d, void* spix, int tid, int nthr) {
-    const int pb = px_bytes(d);
-    stage_in(static_cast<char*>(spix), static_cast<const char*>(p.pred) + size_t(d.rec_off) * pb, H,
-             W * pb, size_t(d.rec_stride) * pb, ud_flip(d), tid, nthr);
+template <int W, int H, int NTHR>
+SVT_HD void stage_pred(const KParams& p, const DevBlock& d, void* spix, int tid) {
+    char* s = static_cast<char*>(spix);
+    char* g = static_cast<char*>(const_cast<void*>(p.pred));
+    if (d.meta & META_BD10)
+        stage_copy<H, W * 2, NTHR, true>(s, g + size_t(d.rec_off) * 2, size_t(d.rec_stride) * 2, ud_flip(d), tid);
+    else
+        stage_copy<H, W, NTHR, true>(s, g + size_t(d.rec_off), size_t(d.rec_stride), ud_flip(d), tid);
 }
-template <int W, int H>
-SVT_HD void unstage_recon(const KParams& p, const DevBlock& d, const void* spix, int tid, int nthr) {
-    const int pb = px_bytes(d);
-    stage_out(static_cast<char*>(p.recon) + size_t(d.rec_off) * pb, static_cast<const char*>(spix), H,
-              W * pb, size_t(d.rec_stride) * pb, ud_flip(d), tid, nthr);
+template <int W, int H, int NTHR>
+SVT_HD void unstage_recon(const KParams& p, const DevBlock& d, const void* spix, int tid) {
+    char* s = static_cast<char*>(const_cast<void*>(spix));
+    char* g = static_cast<char*>(p.recon);
+    if (d.meta & META_BD10)
+        stage_copy<H, W * 2, NTHR, false>(s, g + size_t(d.rec_off) * 2, size_t(d.rec_stride) * 2, ud_flip(d), tid);
+    else
+        stage_copy<H, W, NTHR, false>(s, g + size_t(d.rec_off), size_t(d.rec_stride), ud_flip(d), tid);
 }
 // (iscan + 1) of the classes this size can use, as int32
 template <int W, int H>
@@ -606,7 +615,7 @@ residual_kernel(const __grid_constant__ KParams p, int first_block, int count) {
     const int tb = tid / TPB, tl = tid - tb * TPB;
     int16_t* my_stage = stage + tb * G::SP;
     if (p.stages & STAGE_FWD) {
-        if (tb < nb) stage_residual<W, H>(p, sh.blk[tb], my_stage, tl, TPB);
+        if (tb < nb) stage_residual<W, H, TPB>(p, sh.blk[tb], my_stage, tl);
         if (p.stages & STAGE_QUANT) stage_iscan<W, H>(p, sisc, tid, G::NT);
         g2s_commit_wait();
         __syncthreads();
@@ -622,7 +631,7 @@ residual_kernel(const __grid_constant__ KParams p, int first_block, int count) {
     }
     // the residual is consumed: the prediction block streams into the same bytes while the row
     // phase runs
-    if ((p.stages & STAGE_INV) && tb < nb) stage_pred<W, H>(p, sh.blk[tb], my_stage, tl, TPB);
+    if ((p.stages & STAGE_INV) && tb < nb) stage_pred<W, H, TPB>(p, sh.blk[tb], my_stage, tl);
 #pragma unroll 1
     for (int task = tid; task < G::NB * H; task += G::NT) {
         const int b = task / H, r = task % H;
@@ -647,7 +656,7 @@ residual_kernel(const __grid_constant__ KParams p, int first_block, int count) {
             if (b < nb) phase_inv_col<W, H>(sh.blk[b], c, buf + b * G::BLK, stage + b * G::SP);
         }
         __syncthreads();
-        if (tb < nb) unstage_recon<W, H>(p, sh.blk[tb], my_stage, tl, TPB);
+        if (tb < nb) unstage_recon<W, H, TPB>(p, sh.blk[tb], my_stage, tl);
     }
 }
 

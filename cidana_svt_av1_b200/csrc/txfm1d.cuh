@@ -21,9 +21,11 @@
 #if defined(__CUDACC__)
 #define SVT_HD __host__ __device__ __forceinline__
 #define SVT_TABLE __device__
+#define SVT_NOINLINE static __host__ __device__ __noinline__
 #else
 #define SVT_HD inline __attribute__((always_inline))
 #define SVT_TABLE
+#define SVT_NOINLINE inline
 #endif
 
 namespace svt {

@@ -16,10 +16,10 @@ static void run_size(const KParams& p, int first, int count) {
     for (int i = first; i < first + count; ++i) {
         const DevBlock& d = p.blocks[i];
         if (p.stages & STAGE_FWD) {
-            stage_residual<W, H>(p, d, stage, 0, 1);
+            stage_residual<W, H, 1>(p, d, stage, 0);
             for (int c = 0; c < W; ++c) phase_fwd_col<W, H>(d, c, buf.data(), stage);
         }
-        if (p.stages & STAGE_INV) stage_pred<W, H>(p, d, stage, 0, 1);
+        if (p.stages & STAGE_INV) stage_pred<W, H, 1>(p, d, stage, 0);
         int eob = 0;
         unsigned long long energy = 0;
         QRow q = {};
@@ -35,7 +35,7 @@ static void run_size(const KParams& p, int first, int count) {
         if ((p.stages & STAGE_FWD) && p.energy) p.energy[d.id] = energy;
         if (p.stages & STAGE_INV) {
             for (int c = 0; c < W; ++c) phase_inv_col<W, H>(d, c, buf.data(), stage);
-            unstage_recon<W, H>(p, d, stage, 0, 1);
+            unstage_recon<W, H, 1>(p, d, stage, 0);
         }
     }
 }
