@@ -215,7 +215,12 @@ int svtgpu_run_internal(SvtGpuContext* c, const SvtGpuPlan* pl, const SvtGpuBuff
     // another; a single bucket goes straight onto the caller's stream.
     int nb = 0;
     for (int s = 0; s < 19; ++s) nb += pl->count[s] > 0;
-    if (nb == 1) {
+    static const int n_side = [] {  // tuning knob SVTGPU_SIDE_STREAMS (0 = every bucket on the caller's stream)
+        const char* e = getenv("SVTGPU_SIDE_STREAMS");
+        const int v = e ? atoi(e) : 2;  // measured on B200 (1080p8): 0 -> 0.352, 2 -> 0.314, 4 -> 0.333 ms/step
+        return v < 0 ? 0 : (v > SvtGpuContext::kSide ? SvtGpuContext::kSide : v);
+    }();
+    if (nb == 1 || n_side == 0) {
         for (int s = 0; s < 19; ++s)
             if (pl->count[s]) { CK(launch_bucket(s, p, pl->first[s], pl->count[s], st)); c->launches++; }
         return SVTGPU_OK;
@@ -235,7 +240,7 @@ int svtgpu_run_internal(SvtGpuContext* c, const SvtGpuPlan* pl, const SvtGpuBuff
     for (int i = 0; i < 19; ++i) {
         const int s = order[i];
         if (!pl->count[s]) continue;
-        const int si = k++ % SvtGpuContext::kSide;
+        const int si = k++ % n_side;
         if (!used[si]) { CK(cudaStreamWaitEvent(c->side[si], c->fork, 0)); used[si] = true; }
         CK(launch_bucket(s, p, pl->first[s], pl->count[s], c->side[si]));
         c->launches++;
