@@ -17,6 +17,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libsvtgpu.so")
 
 STAGE_FWD, STAGE_QUANT, STAGE_INV, STAGE_ALL = 1, 2, 4, 7
+STAGE_RESIDUAL = 16  # residual = src - pred on the fly
 
 
 class SvtGpuError(RuntimeError):
@@ -25,7 +26,7 @@ class SvtGpuError(RuntimeError):
 
 class _Buffers(ctypes.Structure):  # SvtGpuBuffers
     _fields_ = [(n, ctypes.c_void_p) for n in ("residual", "pred", "recon", "coeff_in", "coeff",
-                                               "qcoeff", "dqcoeff", "eob", "energy")]
+                                               "qcoeff", "dqcoeff", "eob", "energy", "src", "dist")]
 
 
 class _HostFrame(ctypes.Structure):  # SvtGpuHostFrame
@@ -33,7 +34,8 @@ class _HostFrame(ctypes.Structure):  # SvtGpuHostFrame
                 ("residual", ctypes.c_void_p), ("residual_elems", ctypes.c_size_t),
                 ("pred", ctypes.c_void_p), ("recon", ctypes.c_void_p), ("pixel_elems", ctypes.c_size_t),
                 ("qcoeff", ctypes.c_void_p), ("dqcoeff", ctypes.c_void_p), ("coeff_elems", ctypes.c_size_t),
-                ("eob", ctypes.c_void_p), ("energy", ctypes.c_void_p)]
+                ("eob", ctypes.c_void_p), ("energy", ctypes.c_void_p), ("src", ctypes.c_void_p),
+                ("dist", ctypes.c_void_p)]
 
 
 _lib = None
@@ -151,21 +153,31 @@ class SvtGpu:
         _check(lib().svtgpu_sync(self.handle), "svtgpu_sync")
 
     # ---- the end-to-end call: host buffers in, host buffers out -----------------------------------
-    def host_buffers(self, batch, pinned=True):
+    def host_buffers(self, batch, pinned=True, dist=False, coeffs=True):
         """Output (and page-locked input) buffers a caller of the host pipeline owns: allocate
         once, reuse for every run over batches of this geometry."""
-        return HostBuffers(batch, pinned)
+        return HostBuffers(batch, pinned, dist, coeffs)
 
-    def submit_host(self, frame, out, stages=STAGE_ALL, residual=None, pred=None):
+    def submit_host(self, frame, out, stages=STAGE_ALL, residual=None, pred=None, src=None):
         """Queue one picture (a Batch whose offsets are relative to its own arrays) on the
-        pipeline; `out` is a dict of host arrays (qcoeff, dqcoeff, eob, energy, recon) sized for
-        this picture.  Returns the ticket.  Asynchronous: see svtgpu_submit_host."""
+        pipeline; `out` is a dict of host arrays (qcoeff, dqcoeff, eob, energy, recon and
+        optionally dist) sized for this picture; qcoeff / dqcoeff may be None next to dist.
+        With STAGE_RESIDUAL the residual is source - prediction (`src`, default frame.src).
+        Returns the ticket.  Asynchronous: see svtgpu_submit_host."""
         residual = frame.residual if residual is None else residual
         pred = frame.pred if pred is None else pred
+        if stages & STAGE_RESIDUAL:
+            src = frame.src if src is None else src
+
+        def opt(name):
+            v = out.get(name)
+            return _P(v).value if v is not None else None
         hf = _HostFrame(_P(frame.blocks).value, frame.n_blocks, int(frame.bd),
-                        _P(residual).value, residual.size, _P(pred).value, _P(out["recon"]).value,
-                        pred.size, _P(out["qcoeff"]).value, _P(out["dqcoeff"]).value, frame.n_coeff,
-                        _P(out["eob"]).value, _P(out["energy"]).value if out.get("energy") is not None else None)
+                        _P(residual).value if residual is not None else None,
+                        residual.size if residual is not None else 0, _P(pred).value,
+                        _P(out["recon"]).value, pred.size, opt("qcoeff"), opt("dqcoeff"), frame.n_coeff,
+                        _P(out["eob"]).value, opt("energy"), _P(src).value if src is not None else None,
+                        opt("dist"))
         t = ctypes.c_int(-1)
         _check(lib().svtgpu_submit_host(self.handle, ctypes.byref(hf), int(stages), ctypes.byref(t)),
                "svtgpu_submit_host")
@@ -180,7 +192,8 @@ class SvtGpu:
         then one wait.  Returns a dict of numpy arrays like the oracle runners do."""
         bufs = bufs or HostBuffers(batch, pinned=False)
         for k, fr in enumerate(batch.frames()):
-            self.submit_host(fr, bufs.frame_out(k), stages, *bufs.frame_in(k))
+            res, pred, src = bufs.frame_in(k)
+            self.submit_host(fr, bufs.frame_out(k), stages, res, pred, src)
         self.wait_host()
         return bufs.out
 
@@ -222,13 +235,16 @@ class SvtGpu:
 
 class HostBuffers:
     """Host-side arrays of one batch geometry: outputs always, and page-locked copies of the
-    inputs when `pinned` (what a caller that wants full PCIe speed would hold)."""
+    inputs when `pinned` (what a caller that wants full PCIe speed would hold).
+    dist=True adds the per-block distortion pairs; coeffs=False leaves out qcoeff / dqcoeff
+    (allowed only with dist: the mode-decision shape of the call)."""
 
-    def __init__(self, batch, pinned=True):
+    def __init__(self, batch, pinned=True, dist=False, coeffs=True):
         self.batch = batch
         self.pinned = pinned
         n, nc = batch.n_blocks, batch.n_coeff
         pdt = batch.pred.dtype
+        self._keep = []
 
         def alloc(count, dtype):
             if not pinned:
@@ -238,34 +254,42 @@ class HostBuffers:
             self._keep.append(t)
             return t.numpy().view(dtype)[:count]
 
-        self._keep = []
-        self.out = dict(qcoeff=alloc(nc, np.int32), dqcoeff=alloc(nc, np.int32), eob=alloc(n, np.uint16),
-                        energy=alloc(n, np.uint64), recon=alloc(batch.pred.size, pdt), coeff=None)
-        if pinned:
-            self.residual = alloc(batch.residual.size, np.int16)
-            self.pred = alloc(batch.pred.size, pdt)
-            self.residual[:] = batch.residual
-            self.pred[:] = batch.pred
-        else:
-            self.residual, self.pred = batch.residual, batch.pred
+        def held(a):
+            if a is None or not pinned:
+                return a
+            c = alloc(a.size, a.dtype)
+            c[:] = a
+            return c
+
+        self.out = dict(qcoeff=alloc(nc, np.int32) if coeffs else None,
+                        dqcoeff=alloc(nc, np.int32) if coeffs else None, eob=alloc(n, np.uint16),
+                        energy=alloc(n, np.uint64), recon=alloc(batch.pred.size, pdt), coeff=None,
+                        dist=alloc(2 * n, np.uint64).reshape(n, 2) if dist else None)
+        self.residual, self.pred, self.src = held(batch.residual), held(batch.pred), held(batch.src)
         self._frames = batch.frames()
+
+    def _whole(self, f):
+        return len(self._frames) == 1 and f is self.batch
 
     def frame_in(self, k):
         f = self._frames[k]
-        if len(self._frames) == 1 and f is self.batch:
-            return self.residual, self.pred
-        e0 = f.elem0
-        return self.residual[e0:e0 + f.residual.size], self.pred[e0:e0 + f.pred.size]
+        if self._whole(f):
+            return self.residual, self.pred, self.src
+        e0, e1 = f.elem0, f.elem0 + f.pred.size
+        return self.residual[e0:e1], self.pred[e0:e1], (self.src[e0:e1] if self.src is not None else None)
 
     def frame_out(self, k):
         f = self._frames[k]
-        if len(self._frames) == 1 and f is self.batch:
+        if self._whole(f):
             return self.out
         o = self.out
         b0, c0, e0 = f.block0, f.coeff0, f.elem0
-        return dict(qcoeff=o["qcoeff"][c0:c0 + f.n_coeff], dqcoeff=o["dqcoeff"][c0:c0 + f.n_coeff],
+
+        def cut(name, a, b):
+            return o[name][a:b] if o.get(name) is not None else None
+        return dict(qcoeff=cut("qcoeff", c0, c0 + f.n_coeff), dqcoeff=cut("dqcoeff", c0, c0 + f.n_coeff),
                     eob=o["eob"][b0:b0 + f.n_blocks], energy=o["energy"][b0:b0 + f.n_blocks],
-                    recon=o["recon"][e0:e0 + f.pred.size])
+                    recon=o["recon"][e0:e0 + f.pred.size], dist=cut("dist", b0, b0 + f.n_blocks))
 
 
 # ---- Level B mirrors: the reference's entry points on host numpy arrays ----------------------------

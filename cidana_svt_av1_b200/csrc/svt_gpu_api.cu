@@ -25,27 +25,28 @@ void svtgpu_set_error(const char* fmt, const char* a, const char* b, int line) {
 extern "C" const char* svtgpu_last_error(void) { return g_err; }
 
 // ---- launches ------------------------------------------------------------------------------------
-template <int W, int H, bool QM>
+template <int W, int H, bool QM, bool DIST>
 static cudaError_t launch_size_q(const KParams& p, int first, int count, cudaStream_t st) {
     using G = Geo<W, H>;
     static bool configured[64] = {};  // per device: opt in to > 48 KB of dynamic shared memory
     int dev = 0;
     cudaGetDevice(&dev);
     if (!configured[dev & 63]) {
-        cudaError_t e = cudaFuncSetAttribute(residual_kernel<W, H, QM>,
+        cudaError_t e = cudaFuncSetAttribute(residual_kernel<W, H, QM, DIST>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES);
         if (e != cudaSuccess) return e;
         configured[dev & 63] = true;
     }
     const int grid = (count + G::NB - 1) / G::NB;
-    residual_kernel<W, H, QM><<<grid, G::NT, G::SMEM_BYTES, st>>>(p, first, count);
+    residual_kernel<W, H, QM, DIST><<<grid, G::NT, G::SMEM_BYTES, st>>>(p, first, count);
     return cudaGetLastError();
 }
 template <int W, int H>
 static cudaError_t launch_size(const KParams& p, int first, int count, cudaStream_t st) {
     // the qmatrix variant carries the 64-bit quantizer; keep it out of the common instruction stream
-    return p.qm_wt ? launch_size_q<W, H, true>(p, first, count, st)
-                   : launch_size_q<W, H, false>(p, first, count, st);
+    if (p.dist) return launch_size_q<W, H, false, true>(p, first, count, st);  // flat quantizer only (checked by run)
+    return p.qm_wt ? launch_size_q<W, H, true, false>(p, first, count, st)
+                   : launch_size_q<W, H, false, false>(p, first, count, st);
 }
 static cudaError_t launch_bucket(int tx_size, const KParams& p, int first, int count, cudaStream_t st) {
     switch (tx_size) {
@@ -180,7 +181,7 @@ extern "C" void svtgpu_plan_destroy(SvtGpuPlan* pl) {
 // ---- run -----------------------------------------------------------------------------------------
 extern "C" int svtgpu_run(SvtGpuContext* c, const SvtGpuPlan* pl, const SvtGpuBuffers* b, int stages,
                           void* cuda_stream) {
-    if (stages & ~SVTGPU_STAGE_ALL) return SVTGPU_ERR_ARG;
+    if (stages & ~(SVTGPU_STAGE_ALL | SVTGPU_STAGE_RESIDUAL)) return SVTGPU_ERR_ARG;
     return svtgpu_run_internal(c, pl, b, stages, cuda_stream);
 }
 
@@ -188,10 +189,14 @@ int svtgpu_run_internal(SvtGpuContext* c, const SvtGpuPlan* pl, const SvtGpuBuff
                         void* cuda_stream) {
     if (!c || !pl || !b || pl->ctx != c || !(stages & SVTGPU_STAGE_ALL)) return SVTGPU_ERR_ARG;
     const bool fwd = stages & STAGE_FWD, qnt = stages & STAGE_QUANT, inv = stages & STAGE_INV;
-    if (fwd && !b->residual) return SVTGPU_ERR_ARG;
+    const bool diff = stages & STAGE_RESIDUAL;
+    if (diff && (!fwd || !b->src || !b->pred)) return SVTGPU_ERR_ARG;
+    if (fwd && !diff && !b->residual) return SVTGPU_ERR_ARG;
+    if (b->dist && (!fwd || !qnt || pl->uses_qm)) return SVTGPU_ERR_ARG;
     if (!fwd && !b->coeff_in) return SVTGPU_ERR_ARG;
     if (fwd && !qnt && !b->coeff) return SVTGPU_ERR_ARG;
-    if (qnt && (!b->qcoeff || !b->dqcoeff || !b->eob || !c->d_qtables)) return SVTGPU_ERR_ARG;
+    if (qnt && (!b->eob || !c->d_qtables)) return SVTGPU_ERR_ARG;
+    if (qnt && !b->dist && (!b->qcoeff || !b->dqcoeff)) return SVTGPU_ERR_ARG;  // q/dq optional only next to dist
     if (qnt && pl->max_qrow >= uint32_t(c->n_qrows)) return SVTGPU_ERR_ARG;
     if (inv && (!b->pred || !b->recon)) return SVTGPU_ERR_ARG;
     if (fwd && !qnt && inv) return SVTGPU_ERR_ARG;  // inverse needs dequantized input
@@ -205,6 +210,7 @@ int svtgpu_run_internal(SvtGpuContext* c, const SvtGpuPlan* pl, const SvtGpuBuff
     p.residual = b->residual; p.pred = b->pred; p.recon = b->recon;
     p.coeff_in = b->coeff_in; p.coeff_out = b->coeff; p.qcoeff = b->qcoeff; p.dqcoeff = b->dqcoeff;
     p.eob = b->eob; p.energy = b->energy;
+    p.src = b->src; p.dist = reinterpret_cast<unsigned long long*>(b->dist);
     p.qtables = c->d_qtables; p.iscan = c->d_iscan;
     p.qm_wt = pl->uses_qm ? c->d_qm_wt : nullptr; p.qm_iwt = pl->uses_qm ? c->d_qm_iwt : nullptr;
     memcpy(p.iscan_off, c->iscan_off, sizeof(p.iscan_off));

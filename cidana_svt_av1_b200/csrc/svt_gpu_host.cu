@@ -57,11 +57,13 @@ int slot_wait(HostSlot& s) {
 
 extern "C" int svtgpu_submit_host(SvtGpuContext* c, const SvtGpuHostFrame* f, int stages, int* ticket) {
     if (!c || !f || f->n_blocks < 0 || (f->n_blocks && !f->blocks)) return SVTGPU_ERR_ARG;
-    if (!(stages & SVTGPU_STAGE_ALL) || (stages & ~SVTGPU_STAGE_ALL)) return SVTGPU_ERR_ARG;
+    if (!(stages & SVTGPU_STAGE_ALL) || (stages & ~(SVTGPU_STAGE_ALL | SVTGPU_STAGE_RESIDUAL))) return SVTGPU_ERR_ARG;
     if (f->bit_depth != 8 && f->bit_depth != 10) return SVTGPU_ERR_ARG;
     const bool fwd = stages & STAGE_FWD, qnt = stages & STAGE_QUANT, inv = stages & STAGE_INV;
     if (!fwd || !qnt) return SVTGPU_ERR_ARG;  // the pipeline carries the fused path (optionally without INV)
-    if (!f->residual || !f->qcoeff || !f->dqcoeff || !f->eob) return SVTGPU_ERR_ARG;
+    const bool diff = stages & SVTGPU_STAGE_RESIDUAL;
+    if (!f->eob || (diff ? (!f->src || !f->pred) : !f->residual)) return SVTGPU_ERR_ARG;
+    if (!f->dist && (!f->qcoeff || !f->dqcoeff)) return SVTGPU_ERR_ARG;
     if (inv && (!f->pred || !f->recon)) return SVTGPU_ERR_ARG;
     CK(cudaSetDevice(c->device));
     HostSlot& s = c->host[c->host_next];
@@ -102,8 +104,13 @@ extern "C" int svtgpu_submit_host(SvtGpuContext* c, const SvtGpuHostFrame* f, in
     plan.d_blocks = s.d_blocks;
 
     const size_t px = f->bit_depth == 8 ? 1 : 2;
-    TRY(grow(s.d_res, s.cap_res, f->residual_elems, s.st));
-    if (inv) {
+    if (!diff) TRY(grow(s.d_res, s.cap_res, f->residual_elems, s.st));
+    if (diff) {
+        char* sp = static_cast<char*>(s.d_src);
+        TRY(grow(sp, s.cap_src, f->pixel_elems * px, s.st));
+        s.d_src = sp;
+    }
+    if (inv || diff) {
         char* pix = static_cast<char*>(s.d_pix);
         TRY(grow(pix, s.cap_pix, f->pixel_elems * px, s.st));
         s.d_pix = pix;
@@ -112,28 +119,37 @@ extern "C" int svtgpu_submit_host(SvtGpuContext* c, const SvtGpuHostFrame* f, in
         size_t cap2 = s.cap_coeff;
         TRY(grow(s.d_q, s.cap_coeff, f->coeff_elems, s.st));
         TRY(grow(s.d_dq, cap2, f->coeff_elems, s.st));
-        size_t cap_e = s.cap_n;
+        size_t cap_e = s.cap_n, cap_d = s.cap_n;
         TRY(grow(s.d_eob, s.cap_n, size_t(n), s.st));
         TRY(grow(s.d_energy, cap_e, size_t(n), s.st));
+        if (cap_d) cap_d = cap_d * 2;  // d_dist holds two values per block
+        TRY(grow(s.d_dist, cap_d, size_t(n) * 2, s.st));
     }
 
     CK(cudaMemcpyAsync(s.d_blocks, s.h_blocks, size_t(n) * sizeof(DevBlock), cudaMemcpyHostToDevice, s.st));
-    CK(cudaMemcpyAsync(s.d_res, f->residual, f->residual_elems * sizeof(int16_t), cudaMemcpyHostToDevice, s.st));
-    if (inv) CK(cudaMemcpyAsync(s.d_pix, f->pred, f->pixel_elems * px, cudaMemcpyHostToDevice, s.st));
+    if (diff) CK(cudaMemcpyAsync(s.d_src, f->src, f->pixel_elems * px, cudaMemcpyHostToDevice, s.st));
+    else CK(cudaMemcpyAsync(s.d_res, f->residual, f->residual_elems * sizeof(int16_t), cudaMemcpyHostToDevice, s.st));
+    if (inv || diff) CK(cudaMemcpyAsync(s.d_pix, f->pred, f->pixel_elems * px, cudaMemcpyHostToDevice, s.st));
 
     SvtGpuBuffers b;
     memset(&b, 0, sizeof(b));
     b.residual = s.d_res;
     b.pred = s.d_pix;
     b.recon = s.d_pix;  // in place, like the reference
-    b.qcoeff = s.d_q;
-    b.dqcoeff = s.d_dq;
+    b.qcoeff = f->qcoeff ? s.d_q : nullptr;
+    b.dqcoeff = f->dqcoeff ? s.d_dq : nullptr;
     b.eob = s.d_eob;
     b.energy = s.d_energy;
+    b.src = s.d_src;
+    b.dist = f->dist ? s.d_dist : nullptr;
     TRY(svtgpu_run_internal(c, &plan, &b, stages, s.st));
 
-    CK(cudaMemcpyAsync(f->qcoeff, s.d_q, f->coeff_elems * sizeof(int32_t), cudaMemcpyDeviceToHost, s.st));
-    CK(cudaMemcpyAsync(f->dqcoeff, s.d_dq, f->coeff_elems * sizeof(int32_t), cudaMemcpyDeviceToHost, s.st));
+    if (f->qcoeff)
+        CK(cudaMemcpyAsync(f->qcoeff, s.d_q, f->coeff_elems * sizeof(int32_t), cudaMemcpyDeviceToHost, s.st));
+    if (f->dqcoeff)
+        CK(cudaMemcpyAsync(f->dqcoeff, s.d_dq, f->coeff_elems * sizeof(int32_t), cudaMemcpyDeviceToHost, s.st));
+    if (f->dist)
+        CK(cudaMemcpyAsync(f->dist, s.d_dist, size_t(n) * 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, s.st));
     CK(cudaMemcpyAsync(f->eob, s.d_eob, size_t(n) * sizeof(uint16_t), cudaMemcpyDeviceToHost, s.st));
     if (f->energy)
         CK(cudaMemcpyAsync(f->energy, s.d_energy, size_t(n) * sizeof(uint64_t), cudaMemcpyDeviceToHost, s.st));
@@ -167,6 +183,8 @@ void svtgpu_host_release(SvtGpuContext* c) {
         cudaFree(s.d_dq);
         cudaFree(s.d_eob);
         cudaFree(s.d_energy);
+        cudaFree(s.d_dist);
+        cudaFree(s.d_src);
         cudaEventDestroy(s.done);
         cudaStreamDestroy(s.st);
         s = HostSlot();

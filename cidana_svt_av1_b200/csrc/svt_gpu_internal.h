@@ -36,7 +36,10 @@ struct HostSlot {
     size_t cap_coeff = 0;
     uint16_t* d_eob = nullptr;
     uint64_t* d_energy = nullptr;
+    uint64_t* d_dist = nullptr;
     size_t cap_n = 0;
+    void* d_src = nullptr;  // source pixels (SVTGPU_STAGE_RESIDUAL)
+    size_t cap_src = 0;     // bytes
 };
 
 struct SvtGpuContext {

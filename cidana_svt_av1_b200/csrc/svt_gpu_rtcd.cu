@@ -108,6 +108,7 @@ void run_one(Tls& t, int s, int tx_type, int bd, int stages, bool clamp16) {
     cudaStream_t st = t.ctx->stream;
     CKA(cudaMemcpyAsync(t.plan.d_blocks, t.h_blk, sizeof(DevBlock), cudaMemcpyHostToDevice, st));
     SvtGpuBuffers b;
+    memset(&b, 0, sizeof(b));
     b.residual = t.d_res; b.pred = t.d_pix; b.recon = t.d_pix;
     b.coeff_in = t.d_coeff; b.coeff = t.d_coeff;
     b.qcoeff = t.d_coeff + kMaxPix; b.dqcoeff = t.d_coeff + 2 * kMaxPix;

@@ -57,6 +57,7 @@ class Batch:
         self.name = name
         self.frame_bounds = None  # [(block0, block1, elem0, elem1)] when the batch is made of frames
         self._frames = None
+        self.src = None           # source pixels (same geometry as pred) once with_source() made them
 
     @property
     def n_blocks(self):
@@ -84,9 +85,23 @@ class Batch:
                     f = Batch(blk, self.residual[e0:e1], self.pred[e0:e1],
                               int(CODED[blk["tx_size"]].sum()), self.bd, f"{self.name}[{len(out)}]")
                     f.block0, f.coeff0, f.elem0 = b0, c0, e0
+                    if self.src is not None:
+                        f.src = self.src[e0:e1]
                     out.append(f)
                 self._frames = out
         return self._frames
+
+    def with_source(self):
+        """The same batch as mode decision sees it: source pixels instead of a
+        residual.  src = clip(pred + residual); `residual` is recomputed as src - pred so that the
+        two ways of feeding the path describe the same data."""
+        mval = (1 << self.bd) - 1
+        src = np.clip(self.pred.astype(np.int32) + self.residual, 0, mval).astype(self.pred.dtype)
+        b = Batch(self.blocks, (src.astype(np.int32) - self.pred).astype(np.int16), self.pred, self.n_coeff,
+                  self.bd, self.name + "_src")
+        b.src = src
+        b.frame_bounds = self.frame_bounds
+        return b
 
     def algorithmic_bytes(self):
         """residual 2 B + prediction + q/dq 8 B on the coded part + recon, plus

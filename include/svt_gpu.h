@@ -38,7 +38,10 @@ typedef struct SvtGpuContext SvtGpuContext;
 typedef struct SvtGpuPlan SvtGpuPlan;
 
 enum { SVTGPU_OK = 0, SVTGPU_ERR_ARG = -1, SVTGPU_ERR_CUDA = -2, SVTGPU_ERR_NOMEM = -3 };
-enum { SVTGPU_STAGE_FWD = 1, SVTGPU_STAGE_QUANT = 2, SVTGPU_STAGE_INV = 4, SVTGPU_STAGE_ALL = 7 };
+enum { SVTGPU_STAGE_FWD = 1, SVTGPU_STAGE_QUANT = 2, SVTGPU_STAGE_INV = 4, SVTGPU_STAGE_ALL = 7,
+       /* with STAGE_FWD: residual = src - pred computed on the fly (ResidualKernel,
+        * aom_dsp_rtcd.h:2372; residual_kernel16bit, EbPictureOperators.c:134) instead of read */
+       SVTGPU_STAGE_RESIDUAL = 16 };
 enum { SVTGPU_BLK_CLAMP16 = 1, /* 8-bit C quantizer variant, EbFullLoop.c:86-88 */
        SVTGPU_BLK_USE_QM = 2 /* quantization matrices, EbFullLoop.c:239-296 */ };
 
@@ -68,6 +71,13 @@ typedef struct SvtGpuBuffers {
     int32_t *dqcoeff;
     uint16_t *eob;           /* [n_blocks], indexed like the caller's block list */
     uint64_t *energy;        /* [n_blocks] three_quad_energy (0 unless a 64-point size) */
+    /* SURVEY 8f-1, what mode decision consumes (EbFullLoop.c:763-835): */
+    const void *src;         /* STAGE_RESIDUAL input: source pixels, same type and geometry as pred */
+    uint64_t *dist;          /* optional output [n_blocks][2]: tuFullDistortion {DIST_CALC_RESIDUAL,
+                              * DIST_CALC_PREDICTION} = picture_full_distortion32_bits over the coded
+                              * region (cbf-zero rule on eob), + three_quad_energy, scaled by the tx
+                              * size (EbFullLoop.c:808-835).  Flat quantizer only.  When dist is
+                              * given, qcoeff and/or dqcoeff may be NULL and are then not written. */
 } SvtGpuBuffers;
 
 int svtgpu_create(SvtGpuContext **ctx, int device);
@@ -127,6 +137,9 @@ typedef struct SvtGpuHostFrame {
     size_t coeff_elems;
     uint16_t *eob;           /* n_blocks out */
     uint64_t *energy;        /* n_blocks out, or NULL */
+    const void *src;         /* SVTGPU_STAGE_RESIDUAL: pixel_elems source pixels (residual unused) */
+    uint64_t *dist;          /* optional n_blocks x 2 out (see SvtGpuBuffers.dist); qcoeff / dqcoeff
+                              * may then be NULL: nothing is computed for or copied into them */
 } SvtGpuHostFrame;
 /* returns immediately after queueing; *ticket (optional) identifies the submission */
 int svtgpu_submit_host(SvtGpuContext *ctx, const SvtGpuHostFrame *frame, int stages, int *ticket);

@@ -294,3 +294,37 @@ void ref_get_cfg(int tx_size, int tx_type, int32_t *out /* 16 ints */) {
     out[14] = av1_get_max_eob((TxSize)tx_size);
     out[15] = (int)av1_get_adjusted_tx_size((TxSize)tx_size);
 }
+
+/* ---- the reference's residual and transform-domain distortion kernels ---------- */
+#include "EbPictureOperators.h"
+
+/* ResidualKernel through the RTCD pointer (AVX2 when bound) for 8-bit, residual_kernel16bit
+ * (Codec/EbPictureOperators.c:134) for 16-bit pixels */
+void ref_residual(const void *input, uint32_t input_stride, const void *pred, uint32_t pred_stride,
+                  int16_t *residual, uint32_t residual_stride, int w, int h, int bd) {
+    if (bd == 8)
+        ResidualKernel((uint8_t *)input, input_stride, (uint8_t *)pred, pred_stride, residual,
+                       residual_stride, (uint32_t)w, (uint32_t)h);
+    else
+        residual_kernel16bit((uint16_t *)input, input_stride, (uint16_t *)pred, pred_stride,
+                             residual, residual_stride, (uint32_t)w, (uint32_t)h);
+}
+
+/* the call sequence of Codec/EbFullLoop.c:808-835 for one luma TU */
+void ref_tu_distortion(int32_t *coeff, int32_t *recon_coeff, int tx_size, int eob,
+                       uint64_t three_quad_energy, uint64_t dist[2], int use_avx2) {
+    EbPictureBufferDesc_t a, b;
+    memset(&a, 0, sizeof(a));
+    memset(&b, 0, sizeof(b));
+    a.buffer_y = (uint8_t *)coeff;
+    b.buffer_y = (uint8_t *)recon_coeff;
+    uint64_t y[DIST_CALC_TOTAL], cb[DIST_CALC_TOTAL], cr[DIST_CALC_TOTAL];
+    picture_full_distortion32_bits(&a, 0, 0, &b, 0, 0, (uint32_t)tx_size_wide[tx_size],
+                                   (uint32_t)tx_size_high[tx_size], 0, 0, y, cb, cr, (uint32_t)eob,
+                                   0, 0, COMPONENT_LUMA, use_avx2 ? ASM_AVX2 : ASM_NON_AVX2);
+    y[DIST_CALC_RESIDUAL] += three_quad_energy;
+    y[DIST_CALC_PREDICTION] += three_quad_energy;
+    const int32_t shift = (MAX_TX_SCALE - av1_get_tx_scale((TxSize)tx_size)) * 2;
+    dist[0] = RIGHT_SIGNED_SHIFT(y[DIST_CALC_RESIDUAL], shift);
+    dist[1] = RIGHT_SIGNED_SHIFT(y[DIST_CALC_PREDICTION], shift);
+}

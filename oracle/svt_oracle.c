@@ -584,3 +584,81 @@ void svto_fused_blocks(const SvtoBlock *blk, int first, int last, const int16_t 
     }
     free(coeff);
 }
+
+/* ---- residual from source - prediction, transform-domain distortion ---------- */
+/* residual_kernel_c / residual_kernel16bit (Codec/EbPictureOperators.c:166-191, :134-160):
+ * residual = (int16)input - (int16)pred, element by element. */
+void svto_residual(const void *input, uint32_t input_stride, const void *pred, uint32_t pred_stride,
+                   int16_t *residual, uint32_t residual_stride, int w, int h, int bd) {
+    for (int r = 0; r < h; ++r)
+        for (int c = 0; c < w; ++c) {
+            const int a = bd == 8 ? ((const uint8_t *)input)[(size_t)r * input_stride + c]
+                                  : ((const uint16_t *)input)[(size_t)r * input_stride + c];
+            const int b = bd == 8 ? ((const uint8_t *)pred)[(size_t)r * pred_stride + c]
+                                  : ((const uint16_t *)pred)[(size_t)r * pred_stride + c];
+            residual[(size_t)r * residual_stride + c] = (int16_t)((int16_t)a - (int16_t)b);
+        }
+}
+
+/* The per-TU distortion of the full loop (Codec/EbFullLoop.c:808-835):
+ * picture_full_distortion32_bits (Codec/EbPictureOperators.c:349-402) over the coded
+ * min(w,32) x min(h,32) region -- full_distortion_kernel32_bits (:283-313) when the block has
+ * non-zero coefficients, full_distortion_kernel_cbf_zero32_bits (:318-347) otherwise -- then
+ * += three_quad_energy on both entries and RIGHT_SIGNED_SHIFT by (MAX_TX_SCALE - tx_scale) * 2
+ * with MAX_TX_SCALE = 1 (Codec/EbTransforms.h:40). dist[0] = DIST_CALC_RESIDUAL,
+ * dist[1] = DIST_CALC_PREDICTION. */
+void svto_tu_distortion(const int32_t *coeff, const int32_t *recon_coeff, int tx_size, int eob,
+                        uint64_t three_quad_energy, uint64_t dist[2]) {
+    const int n = svto_max_eob(tx_size);
+    uint64_t res = 0, pred = 0;
+    for (int i = 0; i < n; ++i) {
+        const int64_t c = coeff[i];
+        const int64_t d = c - (int64_t)recon_coeff[i];
+        res += (uint64_t)(d * d);
+        pred += (uint64_t)(c * c);
+    }
+    if (!eob) res = pred;
+    res += three_quad_energy;
+    pred += three_quad_energy;
+    const int shift = (1 - svto_tx_scale(tx_size)) * 2;
+    dist[0] = shift < 0 ? res << -shift : res >> shift;
+    dist[1] = shift < 0 ? pred << -shift : pred >> shift;
+}
+
+/* svto_fused_blocks with the residual taken from source - prediction (src has the geometry of
+ * the prediction / reconstruction planes) and the per-block distortion pair. `recon` holds the
+ * prediction on entry, like svto_fused_blocks. */
+void svto_fused_blocks_md(const SvtoBlock *blk, int first, int last, const void *src, void *recon,
+                          const int16_t *tables, int32_t *qcoeff, int32_t *dqcoeff, uint16_t *eob,
+                          uint64_t *energy, uint64_t *dist, const int16_t *const *scans,
+                          int clamp16) {
+    int32_t *coeff = (int32_t *)malloc(sizeof(int32_t) * 4096);
+    int16_t *res = (int16_t *)malloc(sizeof(int16_t) * 4096);
+    for (int i = first; i < last; ++i) {
+        const SvtoBlock *b = &blk[i];
+        const int w = svto_tx_wide(b->tx_size), h = svto_tx_high(b->tx_size);
+        const int n = svto_max_eob(b->tx_size);
+        const int16_t *t = tables + (size_t)b->qrow * 40;
+        const int16_t *scan = scans[b->tx_size * 3 + svto_scan_class(b->tx_size, b->tx_type)];
+        const size_t px = b->bd == 8 ? 1 : 2;
+        svto_residual((const char *)src + (size_t)b->rec_off * px, b->rec_stride,
+                      (const char *)recon + (size_t)b->rec_off * px, b->rec_stride, res, w, w, h,
+                      b->bd);
+        svto_estimate_transform(res, w, coeff, b->tx_size, b->tx_type, b->bd, &energy[i]);
+        svto_quantize(coeff, n, t, t + 8, t + 16, t + 24, t + 32, qcoeff + b->coeff_off,
+                      dqcoeff + b->coeff_off, &eob[i], scan, svto_tx_scale(b->tx_size), NULL, NULL,
+                      (clamp16 || (b->flags & 1)) && b->bd == 8);
+        svto_tu_distortion(coeff, dqcoeff + b->coeff_off, b->tx_size, eob[i], energy[i],
+                           dist + 2 * (size_t)i);
+        if (eob[i]) {
+            if (b->bd == 8)
+                svto_inv_txfm2d_add8(dqcoeff + b->coeff_off, (uint8_t *)recon + b->rec_off,
+                                     b->rec_stride, b->tx_size, b->tx_type);
+            else
+                svto_inv_txfm2d_add(dqcoeff + b->coeff_off, (uint16_t *)recon + b->rec_off,
+                                    b->rec_stride, b->tx_size, b->tx_type, b->bd);
+        }
+    }
+    free(coeff);
+    free(res);
+}

@@ -82,6 +82,17 @@ void svto_fused_blocks(const SvtoBlock *blk, int first, int last, const int16_t 
                        int clamp16, const uint8_t *wt, const uint8_t *iwt,
                        const int32_t *qm_off /* [2][19] or NULL */);
 
+
+/* SURVEY 8f-1 (residual + distortion fusion): see svt_oracle.c */
+void svto_residual(const void *input, uint32_t input_stride, const void *pred, uint32_t pred_stride,
+                   int16_t *residual, uint32_t residual_stride, int w, int h, int bd);
+void svto_tu_distortion(const int32_t *coeff, const int32_t *recon_coeff, int tx_size, int eob,
+                        uint64_t three_quad_energy, uint64_t dist[2]);
+void svto_fused_blocks_md(const SvtoBlock *blk, int first, int last, const void *src, void *recon,
+                          const int16_t *tables, int32_t *qcoeff, int32_t *dqcoeff, uint16_t *eob,
+                          uint64_t *energy, uint64_t *dist, const int16_t *const *scans,
+                          int clamp16);
+
 #ifdef __cplusplus
 }
 #endif

@@ -13,7 +13,7 @@ _lib = None
 
 class Buffers(ctypes.Structure):  # SvtGpuBuffers, include/svt_gpu.h
     _fields_ = [(n, ctypes.c_void_p) for n in ("residual", "pred", "recon", "coeff_in", "coeff",
-                                               "qcoeff", "dqcoeff", "eob", "energy")]
+                                               "qcoeff", "dqcoeff", "eob", "energy", "src", "dist")]
 
 
 def emul():
@@ -31,14 +31,17 @@ def emul():
     return _lib
 
 
-def run_emul(batch, tables, stages=7, qm=None, coeff_in=None, want_coeff=False):
+def run_emul(batch, tables, stages=7, qm=None, coeff_in=None, want_coeff=False, dist=False, coeffs=True):
     E = emul()
     n = batch.n_blocks
-    out = dict(qcoeff=np.zeros(batch.n_coeff, np.int32), dqcoeff=np.zeros(batch.n_coeff, np.int32),
+    out = dict(qcoeff=np.zeros(batch.n_coeff, np.int32) if coeffs else None,
+               dqcoeff=np.zeros(batch.n_coeff, np.int32) if coeffs else None,
                eob=np.zeros(n, np.uint16), energy=np.zeros(n, np.uint64), recon=batch.pred.copy(),
-               coeff=np.zeros(batch.n_coeff, np.int32) if want_coeff else None)
+               coeff=np.zeros(batch.n_coeff, np.int32) if want_coeff else None,
+               dist=np.zeros((n, 2), np.uint64) if dist else None)
     b = Buffers(P(batch.residual), P(batch.pred), P(out["recon"]), P(coeff_in), P(out["coeff"]),
-                P(out["qcoeff"]), P(out["dqcoeff"]), P(out["eob"]), P(out["energy"]))
+                P(out["qcoeff"]), P(out["dqcoeff"]), P(out["eob"]), P(out["energy"]),
+                P(batch.src) if (stages & 16) else None, P(out["dist"]))
     wt = iwt = off = None
     if qm is not None:
         wt, iwt, off = qm

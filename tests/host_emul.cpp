@@ -24,13 +24,19 @@ static void run_size(const KParams& p, int first, int count) {
         unsigned long long energy = 0;
         QRow q = {};
         if (p.stages & STAGE_QUANT) q = load_qrow<G::LOG_SCALE>(p.qtables + size_t(d.qrow) * 40);
+        unsigned long long dist[2] = { 0, 0 };
         for (int r = 0; r < H; ++r) {
-            int e; unsigned long long en;
-            if (p.qm_wt) phase_row<W, H, true>(p, d, q, r, buf.data(), block_iscan<W, H>(d, isc.data()), e, en);
-            else phase_row<W, H, false>(p, d, q, r, buf.data(), block_iscan<W, H>(d, isc.data()), e, en);
+            int e; unsigned long long en, ds[2];
+            const int* isc_b = block_iscan<W, H>(d, isc.data());
+            if (p.dist) phase_row<W, H, false, true>(p, d, q, r, buf.data(), isc_b, e, en, ds);
+            else if (p.qm_wt) phase_row<W, H, true, false>(p, d, q, r, buf.data(), isc_b, e, en, ds);
+            else phase_row<W, H, false, false>(p, d, q, r, buf.data(), isc_b, e, en, ds);
             eob = e > eob ? e : eob;
             energy += en;
+            dist[0] += ds[0];
+            dist[1] += ds[1];
         }
+        if (p.dist) finish_dist<G::LOG_SCALE>(dist[0], dist[1], eob, energy, p.dist + 2 * size_t(d.id));
         if (p.stages & STAGE_QUANT) p.eob[d.id] = (uint16_t)eob;
         if ((p.stages & STAGE_FWD) && p.energy) p.energy[d.id] = energy;
         if (p.stages & STAGE_INV) {
@@ -67,6 +73,7 @@ extern "C" int emul_run_batch(const SvtGpuBlock* blocks, int n, const SvtGpuBuff
     p.residual = bufs->residual; p.pred = bufs->pred; p.recon = bufs->recon;
     p.coeff_in = bufs->coeff_in; p.coeff_out = bufs->coeff; p.qcoeff = bufs->qcoeff;
     p.dqcoeff = bufs->dqcoeff; p.eob = bufs->eob; p.energy = bufs->energy;
+    p.src = bufs->src; p.dist = reinterpret_cast<unsigned long long*>(bufs->dist);
     p.qtables = qtables; p.iscan = iscan.data(); p.qm_wt = wt; p.qm_iwt = iwt;
     for (int i = 0; i < 2 * 19; ++i) (&p.qm_off[0][0])[i] = qm_off ? qm_off[i] : 0;
     for (int s = 0; s < 19; ++s)

@@ -149,6 +149,36 @@ def run_oracle(batch, tables, scans, clamp16=0, qm=None, threads=1, first=0, las
     return dict(qcoeff=q, dqcoeff=dq, eob=eob, energy=energy, recon=recon)
 
 
+def run_oracle_md(batch, tables, scans, clamp16=0, threads=1):
+    """svto_fused_blocks_md: residual from batch.src - batch.pred, plus the distortion pairs."""
+    import threading
+    O = oracle()
+    n = batch.n_blocks
+    q = np.zeros(batch.n_coeff, np.int32)
+    dq = np.zeros(batch.n_coeff, np.int32)
+    eob = np.zeros(n, np.uint16)
+    energy = np.zeros(n, np.uint64)
+    dist = np.zeros((n, 2), np.uint64)
+    recon = batch.pred.copy()
+    ptrs = (ctypes.c_void_p * (19 * 3))()
+    keep = []
+    for s in range(19):
+        for c in range(3):
+            a = np.ascontiguousarray(scans[(s, c)][0])
+            keep.append(a)
+            ptrs[s * 3 + c] = a.ctypes.data
+    blocks = np.ascontiguousarray(batch.blocks)
+
+    def work(a, b):
+        O.svto_fused_blocks_md(P(blocks), a, b, P(batch.src), P(recon), P(tables), P(q), P(dq), P(eob),
+                               P(energy), P(dist), ptrs, int(clamp16))
+    sl = _slices(n, threads)
+    th = [threading.Thread(target=work, args=x) for x in sl]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    return dict(qcoeff=q, dqcoeff=dq, eob=eob, energy=energy, recon=recon, dist=dist)
+
+
 def run_ref(batch, tables, threads=1, first=0, last=None, asm=1):
     """The compiled reference (AVX2 RTCD table) over the same arrays; no qmatrix, no clamp16."""
     import threading

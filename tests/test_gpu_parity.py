@@ -10,7 +10,7 @@ import pytest
 import cidana_svt_av1_b200 as pkg
 from cidana_svt_av1_b200 import workloads as wl
 from golden_util import load_fused_vectors, load_qmatrices, load_quant_tables, load_scans
-from oracle_lib import P, build_tables, max_eob, qm_pack, run_oracle
+from oracle_lib import P, build_tables, max_eob, qm_pack, run_oracle, run_oracle_md
 
 pytestmark = pytest.mark.gpu
 KEYS = ("qcoeff", "dqcoeff", "eob", "energy", "recon")
@@ -165,6 +165,51 @@ def test_host_pipeline_many_frames_reused_buffers():
     with pytest.raises(pkg.api.SvtGpuError):
         g.submit_host(bb, hb2.frame_out(0))
     g.wait_host()
+
+
+def test_source_minus_prediction_and_distortion():
+    """SURVEY 8f-1 on the device: residual = source - prediction computed while staging
+    (ResidualKernel), per-block distortion pairs (picture_full_distortion32_bits + energy + scaling),
+    with and without the coefficient arrays, through the host pipeline and the batch API."""
+    scans = load_scans()
+    for bd in (8, 10):
+        g = ctx(bd)
+        for qi in ((20,), (255,)):
+            batch = wl.make_packed_batch(wl.valid_pairs(), bd, 9, seed=40 + bd, qindex=qi).with_source()
+            want = run_oracle_md(batch, tables(bd), scans, threads=8)
+            hb = g.host_buffers(batch, pinned=False, dist=True)
+            got = g.run_host(batch, stages=7 | 16, bufs=hb)
+            check(got, want, f"md bd{bd} q{qi}")
+            assert np.array_equal(got["dist"], want["dist"]), np.nonzero(got["dist"] != want["dist"])[0][:5]
+            lean = g.run_host(batch, stages=7 | 16, bufs=g.host_buffers(batch, pinned=False, dist=True, coeffs=False))
+            for k in ("eob", "energy", "recon", "dist"):
+                assert np.array_equal(lean[k], want[k]), k
+            assert lean["qcoeff"] is None
+    # frames (strided planes, flips, mixed sizes), pinned buffers, the plain-residual route with dist
+    g = ctx(8)
+    frame = wl.make_frame_batch(640, 384, 3, 8, seed=11).with_source()
+    want = run_oracle_md(frame, tables(8), scans, threads=8)
+    got = g.run_host(frame, stages=7 | 16, bufs=g.host_buffers(frame, pinned=True, dist=True))
+    check(got, want, "md frames")
+    assert np.array_equal(got["dist"], want["dist"])
+    got2 = g.run_host(frame, stages=7, bufs=g.host_buffers(frame, pinned=True, dist=True))
+    check(got2, want, "dist with a given residual")
+    assert np.array_equal(got2["dist"], want["dist"])
+    # unaligned planes take the per-pixel path
+    odd = wl.make_packed_batch([(2, 0), (0, 5), (7, 9)], 8, 5, seed=3).with_source()
+    odd.src = np.concatenate([np.zeros(3, odd.src.dtype), odd.src])[3:]
+    odd.pred = np.concatenate([np.zeros(1, odd.pred.dtype), odd.pred])[1:]
+    want = run_oracle_md(odd, tables(8), scans)
+    got = g.run_host(odd, stages=7 | 16, bufs=g.host_buffers(odd, pinned=False, dist=True))
+    check(got, want, "md unaligned")
+    assert np.array_equal(got["dist"], want["dist"])
+    # qmatrix + dist is refused
+    qm = qm_pack(load_qmatrices(), 6)
+    gq = ctx(10, qm)
+    bq = wl.make_packed_batch([(1, 0)], 10, 2, seed=1, qindex=(100,), flags=wl.BLK_USE_QM).with_source()
+    with pytest.raises(pkg.api.SvtGpuError):
+        gq.run_host(bq, stages=7 | 16, bufs=gq.host_buffers(bq, pinned=False, dist=True))
+    gq.wait_host()
 
 
 # ---- levels A and B: the reference's own signatures, host pointers ---------------------------------

@@ -9,7 +9,7 @@ import pytest
 from cidana_svt_av1_b200 import workloads as wl
 from emul_lib import emul, run_emul
 from golden_util import load_fused_vectors, load_qmatrices, load_quant_tables, load_scans
-from oracle_lib import P, build_tables, max_eob, oracle, qm_pack, run_oracle
+from oracle_lib import P, build_tables, max_eob, oracle, qm_pack, run_oracle, run_oracle_md
 
 KEYS = ("qcoeff", "dqcoeff", "eob", "energy", "recon")
 
@@ -133,6 +133,32 @@ def test_frame_batch_small():
     batch = wl.make_frame_batch(192, 128, 1, 10, seed=20241, qindex=100, laplace_b=24.0)
     tables = _tables(10)
     _check(run_emul(batch, tables), run_oracle(batch, tables, load_scans()), "frame10")
+
+
+def test_source_minus_prediction_and_distortion():
+    """residual taken as source - prediction while staging, per-block distortion pairs,
+    with and without the coefficient outputs; all sizes and types, both depths, small qindex
+    (eob != 0) and large (mostly eob == 0: the cbf-zero rule), packed and frame layouts."""
+    scans = load_scans()
+    for bd in (8, 10):
+        tables = _tables(bd)
+        for qi in ((20,), (255,)):
+            batch = wl.make_packed_batch(wl.valid_pairs(), bd, 2, seed=40 + bd, qindex=qi).with_source()
+            want = run_oracle_md(batch, tables, scans)
+            # the source route and the residual route describe the same data
+            _check(want, run_oracle(batch, tables, scans), "md oracle vs plain oracle")
+            got = run_emul(batch, tables, stages=7 | 16, dist=True)
+            _check(got, want, f"md emul bd{bd} q{qi}")
+            assert np.array_equal(got["dist"], want["dist"]), np.nonzero(got["dist"] != want["dist"])[0][:5]
+            lean = run_emul(batch, tables, stages=7 | 16, dist=True, coeffs=False)
+            for k in ("eob", "energy", "recon", "dist"):
+                assert np.array_equal(lean[k], want[k]), k
+    frame = wl.make_frame_batch(256, 128, 1, 8, seed=7).with_source()
+    want = run_oracle_md(frame, _tables(8), scans)
+    got = run_emul(frame, _tables(8), stages=7 | 16, dist=True)
+    _check(got, want, "md frame")
+    assert np.array_equal(got["dist"], want["dist"])
+    assert (want["eob"] == 0).any() and (want["eob"] != 0).any()
 
 
 def test_plan_rejects_bad_blocks():

@@ -211,3 +211,46 @@ def test_inverse_recon_all_pairs(bd, asm):
                 R.ref_inv_transform_recon(P(aligned_copy(dq)), P(pa), stride, s, t, 10, eob)
                 O.svto_inv_txfm2d_add(P(dq), P(pb), stride, s, t, 10)
             assert np.array_equal(pa, pb), (s, t, k, asm)
+
+
+# ---- residual = source - prediction, transform-domain distortion ----------------------
+@pytest.mark.parametrize("bd", [8, 10])
+@pytest.mark.parametrize("asm", [0, 1])
+def test_residual_kernel(bd, asm):
+    """svto_residual == ResidualKernel (C / AVX2) and residual_kernel16bit on every block shape."""
+    R, O = ref(asm), oracle()
+    rng = np.random.default_rng(31 + bd)
+    pix = np.uint8 if bd == 8 else np.uint16
+    for s in range(19):
+        w, h = TX_W[s], TX_H[s]
+        stride = 96
+        src = aligned_copy(rng.integers(0, 1 << bd, (h, stride)).astype(pix))
+        prd = aligned_copy(rng.integers(0, 1 << bd, (h, stride)).astype(pix))
+        if s % 3 == 0:  # extremes: full-range differences
+            src[:, :w], prd[:, :w] = (1 << bd) - 1, 0
+            src[::2, :w], prd[::2, :w] = 0, (1 << bd) - 1
+        a = aligned((h, 80), np.int16, fill=7)
+        b = aligned((h, 80), np.int16, fill=7)
+        R.ref_residual(P(src), stride, P(prd), stride, P(a), 80, w, h, bd)
+        O.svto_residual(P(src), stride, P(prd), stride, P(b), 80, w, h, bd)
+        assert np.array_equal(a, b), (s, bd, asm)
+        assert np.array_equal(a[:, :w], src[:, :w].astype(np.int32) - prd[:, :w].astype(np.int32))
+
+
+@pytest.mark.parametrize("asm", [0, 1])
+def test_tu_distortion(asm):
+    """svto_tu_distortion == picture_full_distortion32_bits + energy + shift (EbFullLoop.c:808-835),
+    C and AVX2 kernels, with and without non-zero coefficients, every transform size."""
+    R, O = ref(asm), oracle()
+    rng = np.random.default_rng(77)
+    u64 = ctypes.c_uint64
+    for s in range(19):
+        n = max_eob(s)
+        for amp, eob, energy in ((200, 5, 0), (1 << 17, n, 123456789), (1 << 15, 0, 0), (3, 0, 99)):
+            cf = aligned_copy(rng.integers(-amp, amp + 1, n).astype(np.int32))
+            dq = aligned_copy((cf + rng.integers(-50, 51, n)).astype(np.int32))
+            a = np.zeros(2, np.uint64)
+            b = np.zeros(2, np.uint64)
+            R.ref_tu_distortion(P(cf), P(dq), s, eob, u64(energy), P(a), asm)
+            O.svto_tu_distortion(P(cf), P(dq), s, eob, u64(energy), P(b))
+            assert np.array_equal(a, b), (s, amp, eob, a, b)
