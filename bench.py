@@ -11,6 +11,7 @@ output inside the timed region).  Multi-GPU: one process per GPU, frames sharded
 its own frame batch: weak scaling), no collective on the data path.
 """
 import argparse
+import ctypes
 import json
 import os
 import subprocess
@@ -276,13 +277,21 @@ def gpu_arm(args, rank, world, local_rank):
     def e2e_step():
         g.run_host(batch, bufs=hb)
 
-    e2e_steps = max(2, min(args.steps, 5))
-    e2e_step()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
+    e2e_steps = max(2, min(args.steps, 10))
+    for _ in range(3):  # three passes: every picture of the batch has met every lane of the pipeline
         e2e_step()
     barrier()
+    t0 = time.perf_counter()
+    e2e_each = []
+    L = pkg.api.lib()
+    L.svtgpu_debug_host_allocs.restype = ctypes.c_longlong
+    for _ in range(e2e_steps):
+        t1 = time.perf_counter()
+        e2e_step()
+        e2e_each.append((round((time.perf_counter() - t1) * 1e3, 2), int(L.svtgpu_debug_host_allocs())))
+    barrier()
+    if rank == 0:
+        print("e2e ms per step:", e2e_each, file=sys.stderr, flush=True)
     e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)

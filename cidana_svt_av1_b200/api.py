@@ -14,7 +14,8 @@ import numpy as np
 from .workloads import BLOCK_DTYPE, TX_H, TX_W, coded_count
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libsvtgpu.so")
+# SVTGPU_LIB: another build of the same library (A/B experiments, tools/build_variant.sh)
+LIB_PATH = os.environ.get("SVTGPU_LIB") or os.path.join(HERE, "libsvtgpu.so")
 
 STAGE_FWD, STAGE_QUANT, STAGE_INV, STAGE_ALL = 1, 2, 4, 7
 STAGE_RESIDUAL = 16  # residual = src - pred on the fly

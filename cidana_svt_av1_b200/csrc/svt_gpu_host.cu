@@ -15,14 +15,17 @@ using namespace svt;
 
 namespace {
 
+long long g_host_allocs = 0;  // (re)allocations made by the pipeline: 0 in steady state
+
 template <class T>
-int grow(T*& p, size_t& cap, size_t need, cudaStream_t st) {
+int grow(T*& p, size_t& cap, size_t need, cudaStream_t st, size_t headroom_div = 4) {
     if (need <= cap) return SVTGPU_OK;
+    ++g_host_allocs;
     CK(cudaStreamSynchronize(st));
     if (p) CK(cudaFree(p));
     p = nullptr;
     cap = 0;
-    const size_t want = need + need / 4;
+    const size_t want = need + need / headroom_div;
     if (cudaMalloc(reinterpret_cast<void**>(&p), want * sizeof(T)) != cudaSuccess) {
         cudaGetLastError();
         svtgpu_set_error("%s%s (line %d)", "out of device memory in the host pipeline", "", __LINE__);
@@ -82,11 +85,14 @@ extern "C" int svtgpu_submit_host(SvtGpuContext* c, const SvtGpuHostFrame* f, in
     plan.n = n;
     if (size_t(n) > s.cap_blocks) {
         CK(cudaStreamSynchronize(s.st));
+        ++g_host_allocs;
         if (s.h_blocks) CK(cudaFreeHost(s.h_blocks));
         s.h_blocks = nullptr;
-        CK(cudaMallocHost(reinterpret_cast<void**>(&s.h_blocks), (size_t(n) + n / 4) * sizeof(DevBlock)));
+        CK(cudaMallocHost(reinterpret_cast<void**>(&s.h_blocks), size_t(n) * 2 * sizeof(DevBlock)));
     }
-    TRY(grow(s.d_blocks, s.cap_blocks, size_t(n), s.st));
+    // per-block buffers are small (32 + 26 bytes per block) and the block count of a picture moves
+    // with its partitioning: 2x headroom so that a lane settles after its first picture
+    TRY(grow(s.d_blocks, s.cap_blocks, size_t(n), s.st, 1));
     static thread_local BucketScratch scratch;
     const int bad = bucket_blocks(f->blocks, n, s.h_blocks, plan.first, plan.count, scratch);
     if (bad) {
@@ -120,10 +126,10 @@ extern "C" int svtgpu_submit_host(SvtGpuContext* c, const SvtGpuHostFrame* f, in
         TRY(grow(s.d_q, s.cap_coeff, f->coeff_elems, s.st));
         TRY(grow(s.d_dq, cap2, f->coeff_elems, s.st));
         size_t cap_e = s.cap_n, cap_d = s.cap_n;
-        TRY(grow(s.d_eob, s.cap_n, size_t(n), s.st));
-        TRY(grow(s.d_energy, cap_e, size_t(n), s.st));
+        TRY(grow(s.d_eob, s.cap_n, size_t(n), s.st, 1));
+        TRY(grow(s.d_energy, cap_e, size_t(n), s.st, 1));
         if (cap_d) cap_d = cap_d * 2;  // d_dist holds two values per block
-        TRY(grow(s.d_dist, cap_d, size_t(n) * 2, s.st));
+        TRY(grow(s.d_dist, cap_d, size_t(n) * 2, s.st, 1));
     }
 
     CK(cudaMemcpyAsync(s.d_blocks, s.h_blocks, size_t(n) * sizeof(DevBlock), cudaMemcpyHostToDevice, s.st));
@@ -158,6 +164,8 @@ extern "C" int svtgpu_submit_host(SvtGpuContext* c, const SvtGpuHostFrame* f, in
     s.busy = true;
     return SVTGPU_OK;
 }
+
+extern "C" long long svtgpu_debug_host_allocs(void) { return g_host_allocs; }
 
 extern "C" int svtgpu_wait_host(SvtGpuContext* c, int ticket) {
     if (!c) return SVTGPU_ERR_ARG;

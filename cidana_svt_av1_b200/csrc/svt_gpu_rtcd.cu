@@ -198,6 +198,7 @@ static void quant_slot(const int32_t* coeff_ptr, intptr_t n_coeffs, int32_t skip
                                         t.d_coeff + 2 * kMaxPix, d_eob);
     CKA(cudaGetLastError());
     t.ctx->launches++;
+    ++g_total_launches;
     CKA(cudaMemcpyAsync(t.h_coeff + kMaxPix, t.d_coeff + kMaxPix, n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
     CKA(cudaMemcpyAsync(t.h_coeff + 2 * kMaxPix, t.d_coeff + 2 * kMaxPix, n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
     CKA(cudaMemcpyAsync(t.h_small + 1, t.d_small + 1, sizeof(uint64_t), cudaMemcpyDeviceToHost, st));

@@ -103,6 +103,10 @@ int svtgpu_run(SvtGpuContext *ctx, const SvtGpuPlan *plan, const SvtGpuBuffers *
 int svtgpu_sync(SvtGpuContext *ctx);
 /* kernels launched by this context so far */
 long long svtgpu_launch_count(const SvtGpuContext *ctx);
+/* kernels launched by every context of this process (levels A and B keep one per thread) */
+long long svtgpu_total_launch_count(void);
+/* diagnostics: buffer (re)allocations made so far by the host pipeline (0 in steady state) */
+long long svtgpu_debug_host_allocs(void);
 
 /* thin memory helpers so that a C caller needs no CUDA headers */
 int svtgpu_malloc(SvtGpuContext *ctx, void **dev_ptr, size_t bytes);

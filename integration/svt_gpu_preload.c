@@ -1,0 +1,223 @@
+/*
+ * svt_gpu_preload.c -- LD_PRELOAD installer that puts libsvtgpu.so behind an UNMODIFIED
+ * SvtAv1EncApp / libSvtAv1Enc.so (INTEGRATION.md sections 1 and 2).
+ *
+ *   LD_PRELOAD=libsvtgpu_preload.so SVT_GPU_LIB=/path/libsvtgpu.so SvtAv1EncApp -i ... -b out.ivf
+ *
+ * Level A (always; needs no reference header): eb_init_encoder is interposed; after the real one
+ * has run setup_rtcd_internal (Source/Lib/Encoder/Codec/EbEncHandle.c:917, before any worker
+ * thread exists, :1796) every RTCD pointer listed by svtgpu_rtcd_table() is overwritten with its
+ * svtgpu_ twin (the pointers are exported globals of the encoder library,
+ * Source/Lib/Common/Codec/aom_dsp_rtcd.h:158-423).
+ *
+ * Level B (built with -DSVT_GPU_LEVEL_B against the reference headers, because
+ * av1_quantize_inv_quantize takes a PictureControlSet): the four entry points
+ * av1_estimate_transform / av1_quantize_inv_quantize / av1_inv_transform_recon[8bit]
+ * (Source/Lib/Common/Codec/EbTransforms.h:3896-3987) are interposed as symbols -- the encoder
+ * library is -fPIC without -Bsymbolic, so its own calls go through the PLT -- and forwarded to
+ * the svtgpu_ entry points.  This also covers the (size, type) pairs for which
+ * av1_estimate_transform hard-wires the _c transform and never consults the RTCD pointer
+ * (EbTransforms.c:4951-5235).
+ *
+ * SVT_GPU_LEVEL = "A", "B" or "AB" (default "AB" when level B is compiled in, else "A").
+ * There is no fallback: if the library or a symbol is missing the process aborts.
+ */
+#define _GNU_SOURCE
+#include <dlfcn.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#ifdef SVT_GPU_LEVEL_B
+#include "EbDefinitions.h"
+#include "EbPictureControlSet.h"
+#include "EbTransforms.h"
+#include "EbSvtAv1Enc.h"
+#endif
+#include "svt_gpu.h"
+
+static void *g_lib;
+static int g_level_a, g_level_b;
+static long long g_calls[4]; /* estimate_transform, quantize_inv_quantize, recon, recon8bit */
+
+static void die(const char *what, const char *arg) {
+    fprintf(stderr, "[svtgpu-preload] %s %s\n", what, arg ? arg : "");
+    abort();
+}
+static void *need(const char *name) {
+    void *p = dlsym(g_lib, name);
+    if (!p) die("libsvtgpu.so does not export", name);
+    return p;
+}
+
+static int (*p_estimate)(int16_t *, uint32_t, int32_t *, uint32_t, uint8_t, uint64_t *, int16_t *,
+                         uint32_t, uint8_t, int, int, int);
+static void (*p_quant)(const int16_t *, const int16_t *, const int16_t *, const int16_t *,
+                       const int16_t *, int32_t *, int32_t *, int32_t *, uint8_t, uint16_t *,
+                       uint32_t *, uint32_t, uint8_t, int);
+static int (*p_recon)(int32_t *, uint8_t *, uint32_t, uint8_t, uint32_t, uint8_t, int, uint32_t);
+static int (*p_recon8)(int32_t *, uint8_t *, uint32_t, uint8_t, uint8_t, int, uint32_t);
+
+static long long (*p_launches)(void);
+__attribute__((destructor)) static void report(void) {
+    if (!g_lib) return;
+    fprintf(stderr, "[svtgpu-preload] kernels launched by libsvtgpu.so: %lld; level-B calls served: "
+            "estimate_transform %lld, quantize_inv_quantize %lld, inv_transform_recon %lld, "
+            "inv_transform_recon8bit %lld\n", p_launches ? p_launches() : -1,
+            g_calls[0], g_calls[1], g_calls[2], g_calls[3]);
+}
+
+static void install(void) {
+    const char *path = getenv("SVT_GPU_LIB");
+    const char *lvl = getenv("SVT_GPU_LEVEL");
+#ifdef SVT_GPU_LEVEL_B
+    if (!lvl) lvl = "AB";
+#else
+    if (!lvl) lvl = "A";
+#endif
+    g_lib = dlopen(path ? path : "libsvtgpu.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!g_lib) die("cannot load libsvtgpu.so:", dlerror());
+    p_launches = (long long (*)(void))need("svtgpu_total_launch_count");
+    if (strchr(lvl, 'A')) {
+        int (*table)(const SvtGpuRtcdEntry **) = (int (*)(const SvtGpuRtcdEntry **))need("svtgpu_rtcd_table");
+        const SvtGpuRtcdEntry *e = NULL;
+        const int n = table(&e);
+        for (int i = 0; i < n; ++i) {
+            void **slot = (void **)dlsym(RTLD_DEFAULT, e[i].slot);
+            if (!slot) die("the encoder does not export the RTCD pointer", e[i].slot);
+            *slot = e[i].fn;
+        }
+        g_level_a = n;
+    }
+    if (strchr(lvl, 'B')) {
+#ifdef SVT_GPU_LEVEL_B
+        p_estimate = need("svtgpu_av1_estimate_transform");
+        p_quant = need("svtgpu_av1_quantize_inv_quantize");
+        p_recon = need("svtgpu_av1_inv_transform_recon");
+        p_recon8 = need("svtgpu_av1_inv_transform_recon8bit");
+        g_level_b = 1;
+#else
+        die("built without -DSVT_GPU_LEVEL_B; SVT_GPU_LEVEL =", lvl);
+#endif
+    }
+    fprintf(stderr, "[svtgpu-preload] %d RTCD slots rebound to libsvtgpu.so, level-B entry points %s\n",
+            g_level_a, g_level_b ? "interposed" : "left to the encoder");
+}
+
+/* EbSvtAv1Enc.h:439 -- EbErrorType eb_init_encoder(EbComponentType *svt_enc_component) */
+#ifdef SVT_GPU_LEVEL_B
+EbErrorType eb_init_encoder(EbComponentType *svt_enc_component) {
+#else
+int eb_init_encoder(void *svt_enc_component) {
+#endif
+    int (*real)(void *) = (int (*)(void *))dlsym(RTLD_NEXT, "eb_init_encoder");
+    if (!real) die("no eb_init_encoder behind the preload", NULL);
+    const int rc = real(svt_enc_component);
+    if (rc == 0 && !g_lib) install();
+    return rc;
+}
+
+#ifdef SVT_GPU_LEVEL_B
+EbErrorType av1_estimate_transform(int16_t *residual_buffer, uint32_t residual_stride,
+                                   int32_t *coeff_buffer, uint32_t coeff_stride, TxSize transform_size,
+                                   uint64_t *three_quad_energy, int16_t *transform_inner_array_ptr,
+                                   uint32_t bit_increment, TxType transform_type, EbAsm asm_type,
+                                   PLANE_TYPE component_type, EB_TRANS_COEFF_SHAPE trans_coeff_shape) {
+    if (!g_level_b) {
+        static EbErrorType (*real)(int16_t *, uint32_t, int32_t *, uint32_t, TxSize, uint64_t *, int16_t *,
+                                   uint32_t, TxType, EbAsm, PLANE_TYPE, EB_TRANS_COEFF_SHAPE);
+        if (!real) real = dlsym(RTLD_NEXT, "av1_estimate_transform");
+        return real(residual_buffer, residual_stride, coeff_buffer, coeff_stride, transform_size,
+                    three_quad_energy, transform_inner_array_ptr, bit_increment, transform_type,
+                    asm_type, component_type, trans_coeff_shape);
+    }
+    __atomic_fetch_add(&g_calls[0], 1, __ATOMIC_RELAXED);
+    return (EbErrorType)p_estimate(residual_buffer, residual_stride, coeff_buffer, coeff_stride,
+                                   transform_size, three_quad_energy, transform_inner_array_ptr,
+                                   bit_increment, transform_type, asm_type, component_type,
+                                   trans_coeff_shape);
+}
+
+void av1_quantize_inv_quantize(PictureControlSet_t *picture_control_set_ptr, int32_t *coeff,
+                               const uint32_t coeff_stride, int32_t *quant_coeff, int32_t *recon_coeff,
+                               uint32_t qp, uint32_t width, uint32_t height, TxSize txsize, uint16_t *eob,
+                               MacroblockPlane candidate_plane, EbAsm asm_type,
+                               uint32_t *y_count_non_zero_coeffs,
+#if !PF_N2_32X32
+                               EbPfMode pf_mode,
+#endif
+                               uint8_t enable_contouring_qc_update_flag, uint32_t component_type,
+                               uint32_t bit_increment, TxType tx_type, EbBool clean_sparse_coeff_flag) {
+    if (!g_level_b) {
+        static void (*real)(PictureControlSet_t *, int32_t *, const uint32_t, int32_t *, int32_t *, uint32_t,
+                            uint32_t, uint32_t, TxSize, uint16_t *, MacroblockPlane, EbAsm, uint32_t *,
+#if !PF_N2_32X32
+                            EbPfMode,
+#endif
+                            uint8_t, uint32_t, uint32_t, TxType, EbBool);
+        if (!real) real = dlsym(RTLD_NEXT, "av1_quantize_inv_quantize");
+        real(picture_control_set_ptr, coeff, coeff_stride, quant_coeff, recon_coeff, qp, width, height,
+             txsize, eob, candidate_plane, asm_type, y_count_non_zero_coeffs,
+#if !PF_N2_32X32
+             pf_mode,
+#endif
+             enable_contouring_qc_update_flag, component_type, bit_increment, tx_type,
+             clean_sparse_coeff_flag);
+        return;
+    }
+    /* The accessor: the only thing the reference needs the PictureControlSet for
+     * (av1_quantize_inv_quantize_ii, EbFullLoop.c:546-613).  8-bit reads the *Md tables.  For
+     * COMPONENT_CHROMA_CB the reference fills in only quant / dequant and leaves the other rows
+     * to whatever the previous call left in the local (:568-572); the rows of the same plane
+     * are passed here, which is the same data whenever the chroma delta-q values are 0 (they
+     * always are in this encoder: av1_build_quantizer is called with zeros,
+     * EbModeDecisionConfigurationProcess.c). */
+    const PictureParentControlSet_t *p = picture_control_set_ptr->parent_pcs_ptr;
+    const uint32_t q = p->base_qindex;
+    const Quants *qs = bit_increment ? &p->quants : &p->quantsMd;
+    const Dequants *dq = bit_increment ? &p->deq : &p->deqMd;
+    const int16_t *zbin, *round, *quant, *shift, *deq;
+    if (component_type == COMPONENT_LUMA) {
+        zbin = qs->y_zbin[q]; round = qs->y_round[q]; quant = qs->y_quant[q];
+        shift = qs->y_quant_shift[q]; deq = dq->y_dequant_QTX[q];
+    } else if (component_type == COMPONENT_CHROMA_CB) {
+        zbin = qs->u_zbin[q]; round = qs->u_round[q]; quant = qs->u_quant[q];
+        shift = qs->u_quant_shift[q]; deq = p->deq.u_dequant_QTX[q];
+    } else {
+        qs = &p->quants;
+        zbin = qs->v_zbin[q]; round = qs->v_round[q]; quant = qs->v_quant[q];
+        shift = qs->v_quant_shift[q]; deq = p->deq.v_dequant_QTX[q];
+    }
+    __atomic_fetch_add(&g_calls[1], 1, __ATOMIC_RELAXED);
+    p_quant(zbin, round, quant, shift, deq, coeff, quant_coeff, recon_coeff, txsize, eob,
+            y_count_non_zero_coeffs, bit_increment, tx_type, /*clamp16=*/0);
+}
+
+EbErrorType av1_inv_transform_recon(int32_t *coeff_buffer, uint8_t *recon_buffer, uint32_t recon_stride,
+                                    TxSize txsize, uint32_t bit_increment, TxType transform_type,
+                                    PLANE_TYPE component_type, uint32_t eob) {
+    if (!g_level_b) {
+        static EbErrorType (*real)(int32_t *, uint8_t *, uint32_t, TxSize, uint32_t, TxType, PLANE_TYPE, uint32_t);
+        if (!real) real = dlsym(RTLD_NEXT, "av1_inv_transform_recon");
+        return real(coeff_buffer, recon_buffer, recon_stride, txsize, bit_increment, transform_type,
+                    component_type, eob);
+    }
+    __atomic_fetch_add(&g_calls[2], 1, __ATOMIC_RELAXED);
+    return (EbErrorType)p_recon(coeff_buffer, recon_buffer, recon_stride, txsize, bit_increment,
+                                transform_type, component_type, eob);
+}
+
+EbErrorType av1_inv_transform_recon8bit(int32_t *coeff_buffer, uint8_t *recon_buffer, uint32_t recon_stride,
+                                        TxSize txsize, TxType transform_type, PLANE_TYPE component_type,
+                                        uint32_t eob) {
+    if (!g_level_b) {
+        static EbErrorType (*real)(int32_t *, uint8_t *, uint32_t, TxSize, TxType, PLANE_TYPE, uint32_t);
+        if (!real) real = dlsym(RTLD_NEXT, "av1_inv_transform_recon8bit");
+        return real(coeff_buffer, recon_buffer, recon_stride, txsize, transform_type, component_type, eob);
+    }
+    __atomic_fetch_add(&g_calls[3], 1, __ATOMIC_RELAXED);
+    return (EbErrorType)p_recon8(coeff_buffer, recon_buffer, recon_stride, txsize, transform_type,
+                                 component_type, eob);
+}
+#endif /* SVT_GPU_LEVEL_B */

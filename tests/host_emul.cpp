@@ -10,9 +10,7 @@ template <int W, int H>
 static void run_size(const KParams& p, int first, int count) {
     using G = Geo<W, H>;
     std::vector<int> buf(G::BLK);
-    std::vector<int> isc(G::ISC_WORDS);
     alignas(16) static thread_local int16_t stage[64 * 64];
-    if (p.stages & STAGE_QUANT) stage_iscan<W, H>(p, isc.data(), 0, 1);
     for (int i = first; i < first + count; ++i) {
         const DevBlock& d = p.blocks[i];
         if (p.stages & STAGE_FWD) {
@@ -27,7 +25,7 @@ static void run_size(const KParams& p, int first, int count) {
         unsigned long long dist[2] = { 0, 0 };
         for (int r = 0; r < H; ++r) {
             int e; unsigned long long en, ds[2];
-            const int* isc_b = block_iscan<W, H>(d, isc.data());
+            const int16_t* isc_b = block_iscan<W, H>(p, d);
             if (p.dist) phase_row<W, H, false, true>(p, d, q, r, buf.data(), isc_b, e, en, ds);
             else if (p.qm_wt) phase_row<W, H, true, false>(p, d, q, r, buf.data(), isc_b, e, en, ds);
             else phase_row<W, H, false, false>(p, d, q, r, buf.data(), isc_b, e, en, ds);

@@ -1,0 +1,92 @@
+"""SURVEY 8f-3 / BASELINE configs 1 and 5 (scaled to what one-block-per-call latency allows): the
+UNMODIFIED reference encoder application (oracle/_ref/SvtAv1EncApp, built from the reference's
+own sources by `make -C oracle encapp`) encodes the same synthetic clip twice -- once as it is
+(C/AVX2 transform + quantiser path), once with integration/svt_gpu_preload.c rebinding its RTCD
+slots and entry points to libsvtgpu.so -- and the two .ivf bitstreams must be byte-identical.
+
+Test infrastructure: the encoder binaries live under oracle/_ref/ (git-ignored, they travel to the
+GPU box with the snapshot); /root/reference is not needed at run time."""
+import hashlib
+import os
+import subprocess
+import time
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REFDIR = os.path.join(ROOT, "oracle", "_ref")
+APP = os.path.join(REFDIR, "SvtAv1EncApp")
+PRELOAD = os.path.join(REFDIR, "libsvtgpu_preload.so")
+GPULIB = os.path.join(ROOT, "cidana_svt_av1_b200", "libsvtgpu.so")
+
+
+def make_clip(path, w, h, n, seed=5):
+    """Moving sinusoid pattern + noise, 4:2:0 8-bit planar."""
+    rng = np.random.default_rng(seed)
+    yy, xx = np.mgrid[0:h, 0:w]
+    with open(path, "wb") as f:
+        for t in range(n):
+            y = 128 + 60 * np.sin((xx + 3 * t) / 17.0) + 40 * np.cos((yy - 2 * t) / 11.0) + rng.normal(0, 6, (h, w))
+            u = 128 + 30 * np.sin((xx[::2, ::2] + t) / 23.0)
+            v = 128 + 30 * np.cos((yy[::2, ::2] + t) / 19.0)
+            for p in (y, u, v):
+                f.write(np.clip(p, 0, 255).astype(np.uint8).tobytes())
+
+
+def encode(clip, out, w, h, n, qp, gpu_level=None, timeout=900):
+    env = dict(os.environ)
+    if gpu_level:
+        env.update(LD_PRELOAD=PRELOAD, SVT_GPU_LIB=GPULIB, SVT_GPU_LEVEL=gpu_level)
+    cmd = [APP, "-i", clip, "-w", str(w), "-h", str(h), "-n", str(n), "-enc-mode", "8", "-q", str(qp),
+           "-b", out]
+    t0 = time.time()
+    r = subprocess.run(cmd, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True,
+                       timeout=timeout)
+    assert r.returncode == 0 and os.path.getsize(out) > 32, r.stdout[-2000:]
+    return time.time() - t0, r.stdout
+
+
+def md5(path):
+    return hashlib.md5(open(path, "rb").read()).hexdigest()
+
+
+needs_app = pytest.mark.skipif(not (os.path.exists(APP) and os.path.exists(PRELOAD)),
+                               reason="oracle/_ref/SvtAv1EncApp not built (make -C oracle encapp needs /root/reference)")
+
+
+@needs_app
+def test_reference_encoder_is_deterministic(tmp_path):
+    """Config 1 at small scale, CPU only: the oracle application itself, twice."""
+    clip = str(tmp_path / "clip.yuv")
+    make_clip(clip, 192, 128, 3)
+    encode(clip, str(tmp_path / "a.ivf"), 192, 128, 3, 30)
+    encode(clip, str(tmp_path / "b.ivf"), 192, 128, 3, 30)
+    assert md5(str(tmp_path / "a.ivf")) == md5(str(tmp_path / "b.ivf"))
+
+
+@needs_app
+def test_preload_fails_loudly_without_the_library(tmp_path):
+    clip = str(tmp_path / "clip.yuv")
+    make_clip(clip, 192, 128, 2)
+    env = dict(os.environ, LD_PRELOAD=PRELOAD, SVT_GPU_LIB=str(tmp_path / "missing.so"))
+    r = subprocess.run([APP, "-i", clip, "-w", "192", "-h", "128", "-n", "2", "-enc-mode", "8", "-b",
+                        str(tmp_path / "x.ivf")], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT,
+                       text=True, timeout=120)
+    assert r.returncode != 0 and "cannot load libsvtgpu.so" in r.stdout
+
+
+@pytest.mark.gpu
+@needs_app
+@pytest.mark.parametrize("level,w,h,n,qp", [("A", 320, 192, 6, 30), ("AB", 320, 192, 6, 30),
+                                            ("AB", 640, 384, 4, 45)])
+def test_bitstream_identical_with_gpu_path(tmp_path, level, w, h, n, qp):
+    clip = str(tmp_path / "clip.yuv")
+    make_clip(clip, w, h, n)
+    ref, gpu = str(tmp_path / "ref.ivf"), str(tmp_path / "gpu.ivf")
+    t_ref, _ = encode(clip, ref, w, h, n, qp)
+    t_gpu, log = encode(clip, gpu, w, h, n, qp, gpu_level=level)
+    assert "RTCD slots rebound" in log, log[-2000:]
+    print(f"\n{w}x{h} x{n} q{qp} level {level}: reference {t_ref:.1f} s, GPU path {t_gpu:.1f} s, "
+          f"{os.path.getsize(ref)} bytes\n" + "\n".join(l for l in log.splitlines() if "svtgpu" in l))
+    assert open(ref, "rb").read() == open(gpu, "rb").read()

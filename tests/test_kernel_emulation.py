@@ -43,6 +43,16 @@ def test_generated_scans_match_av1_scan_orders():
             assert np.array_equal(out, scans[(s, c)][1]), (s, c)
 
 
+def test_iscan_grows_along_every_row():
+    """The kernel takes a row's eob candidate from its LAST non-zero column (row_k in
+    residual_kernel.cuh); that is only the maximum of iscan over the row's non-zero positions
+    if iscan grows with the column index, for every size and scan class of av1_scan_orders."""
+    for (s, cls), (_, iscan) in load_scans().items():
+        kw, kh = min(int(wl.TX_W[s]), 32), min(int(wl.TX_H[s]), 32)
+        m = iscan.astype(np.int64).reshape(kh, kw)
+        assert (np.diff(m, axis=1) > 0).all(), (s, cls)
+
+
 @pytest.mark.parametrize("bd", [8, 10])
 @pytest.mark.parametrize("strided", [False, True])
 def test_fused_all_pairs(bd, strided):
