@@ -60,7 +60,7 @@ static int (*p_recon)(int32_t *, uint8_t *, uint32_t, uint8_t, uint32_t, uint8_t
 static int (*p_recon8)(int32_t *, uint8_t *, uint32_t, uint8_t, uint8_t, int, uint32_t);
 
 static long long (*p_launches)(void);
-__attribute__((destructor)) static void report(void) {
+static void report(void) {
     if (!g_lib) return;
     fprintf(stderr, "[svtgpu-preload] kernels launched by libsvtgpu.so: %lld; level-B calls served: "
             "estimate_transform %lld, quantize_inv_quantize %lld, inv_transform_recon %lld, "
@@ -116,6 +116,19 @@ int eb_init_encoder(void *svt_enc_component) {
     const int rc = real(svt_enc_component);
     if (rc == 0 && !g_lib) install();
     return rc;
+}
+
+/* EbSvtAv1Enc.h -- EbErrorType eb_deinit_encoder(EbComponentType *): the application closes its
+ * log files right after this call, so the usage report is printed here */
+#ifdef SVT_GPU_LEVEL_B
+EbErrorType eb_deinit_encoder(EbComponentType *svt_enc_component) {
+#else
+int eb_deinit_encoder(void *svt_enc_component) {
+#endif
+    int (*real)(void *) = (int (*)(void *))dlsym(RTLD_NEXT, "eb_deinit_encoder");
+    if (!real) die("no eb_deinit_encoder behind the preload", NULL);
+    report();
+    return real(svt_enc_component);
 }
 
 #ifdef SVT_GPU_LEVEL_B
