@@ -198,6 +198,24 @@ class SvtGpu:
         self.wait_host()
         return bufs.out
 
+    def tx_search(self, batch, is_inter=0, reduced_tx_set_used=0, tx_search_reduced_set=0,
+                  want_coeff=False):
+        """SURVEY 8f-2, ProductFullLoopTxSearch (EbFullLoop.c:927-1100) for every block of `batch`
+        at once: each block is expanded into one candidate per tx type the reference would try
+        (svtgpu_tx_search_expand) and all candidates go through one run of forward -> quantise
+        with the distortion outputs.  `batch.src` given: residual = src - pred on the fly.
+        Returns dict(cand_block, tx_type, eob, dist[, qcoeff, coeff_off]) per candidate; a
+        candidate with eob == 0 and tx_type != DCT_DCT is one the reference skips (:1030)."""
+        cand = tx_search_candidates(batch, is_inter, reduced_tx_set_used, tx_search_reduced_set, want_coeff)
+        stages = STAGE_FWD | STAGE_QUANT | (STAGE_RESIDUAL if batch.src is not None else 0)
+        bufs = HostBuffers(cand, pinned=False, dist=True, coeffs=want_coeff)
+        out = self.run_host(cand, stages, bufs)
+        res = dict(cand_block=cand.cand_block, tx_type=cand.blocks["tx_type"].copy(), eob=out["eob"],
+                   dist=out["dist"])
+        if want_coeff:
+            res.update(qcoeff=out["qcoeff"], coeff_off=cand.blocks["coeff_off"].copy())
+        return res
+
     def run_staged(self, batch, stages=STAGE_ALL, want_coeff=False, coeff_in=None, plan=None):
         """Any stage combination through the batch API (svtgpu_plan_create + svtgpu_run) on
         torch-allocated device buffers, synchronous: upload, run, download everything.  Used
@@ -232,6 +250,37 @@ class SvtGpu:
         if own_plan:
             plan.close()
         return out
+
+
+def tx_search_mask(tx_size, is_inter=0, reduced_tx_set_used=0, tx_search_reduced_set=0):
+    """Bit t set = ProductFullLoopTxSearch evaluates tx type t for this size (host only)."""
+    L = lib()
+    L.svtgpu_tx_search_mask.restype = ctypes.c_uint32
+    return int(L.svtgpu_tx_search_mask(int(tx_size), int(is_inter), int(reduced_tx_set_used),
+                                       int(tx_search_reduced_set)))
+
+
+def tx_search_candidates(batch, is_inter=0, reduced_tx_set_used=0, tx_search_reduced_set=0,
+                         want_coeff=False, expand=None):
+    """The candidate batch of a tx-type search: same arrays as `batch`, one block per (block, tried
+    type), `cand_block[k]` = the block candidate k belongs to.  `expand` defaults to the
+    library's svtgpu_tx_search_expand (tests pass the host-emulation twin)."""
+    from .workloads import Batch
+    expand = expand or lib().svtgpu_tx_search_expand
+    blocks = np.ascontiguousarray(batch.blocks)
+    n = len(blocks)
+    cand = np.zeros(16 * max(n, 1), BLOCK_DTYPE)
+    owner = np.zeros(16 * max(n, 1), np.int32)
+    elems = ctypes.c_int64(0)
+    k = expand(_P(blocks), n, int(is_inter), int(reduced_tx_set_used), int(tx_search_reduced_set),
+               int(bool(want_coeff)), _P(cand), _P(owner), ctypes.byref(elems))
+    if k < 0:
+        raise SvtGpuError(f"svtgpu_tx_search_expand failed ({k})")
+    c = Batch(cand[:k].copy(), batch.residual, batch.pred, max(int(elems.value), 4), batch.bd,
+              batch.name + "_txsearch")
+    c.src = batch.src
+    c.cand_block = owner[:k].copy()
+    return c
 
 
 class HostBuffers:

@@ -25,6 +25,64 @@ inline bool tx_pair_valid(int s, int t) {
     return true;
 }
 
+// ---- tx-type search: which types ProductFullLoopTxSearch evaluates -------------------
+// Bit t of the result = tx type t is tried for a luma block of `tx_size`
+// (Source/Lib/Common/Codec/EbFullLoop.c:946-982):
+//   * the type must belong to the extended-tx set of the size: get_ext_tx_set_type +
+//     av1_ext_tx_used (EbDefinitions.h:1472-1500) -- DCT only above 32x32 (square-up), DCT (+IDTX
+//     for inter) at 32x32, otherwise by intra/inter, the reduced-set flag and whether the
+//     square-down size is 16x16;
+//   * with tx_search_reduced_set the encoder's own shortlist allowed_tx_set_a
+//     (EbFullLoop.c:883-902) is applied on top;
+//   * a size whose set comes out empty still tries DCT_DCT (:973-975).
+inline uint32_t tx_search_mask(int tx_size, int is_inter, int reduced_tx_set_used, int tx_search_reduced_set) {
+    if (tx_size < 0 || tx_size > 18) return 0;
+    enum : uint32_t { DCTONLY = 0x0001, DCT_IDTX = 0x0201, DTT4_IDTX = 0x020F, DTT4_IDTX_1DDCT = 0x0E0F,
+                      DTT9_IDTX_1DDCT = 0x0FFF, ALL16 = 0xFFFF };
+    const int w = kTxW[tx_size], h = kTxH[tx_size];
+    const int up = w > h ? w : h, down = w < h ? w : h;  // txsize_sqr_up_map / txsize_sqr_map
+    uint32_t set;
+    if (up > 32) set = DCTONLY;
+    else if (up == 32) set = is_inter ? DCT_IDTX : DCTONLY;
+    else if (reduced_tx_set_used) set = is_inter ? DCT_IDTX : DTT4_IDTX;
+    else if (is_inter) set = down == 16 ? DTT9_IDTX_1DDCT : ALL16;
+    else set = down == 16 ? DTT4_IDTX : DTT4_IDTX_1DDCT;
+    if (tx_search_reduced_set) {
+        // allowed_tx_set_a, one mask per TxSize: the four DCT/ADST combinations + IDTX, V_DCT, H_DCT
+        // for the small sizes (8x8 and 8x16 add V_ADST / H_ADST, 16x8 adds V_ADST / V_FLIPADST),
+        // {DCT_DCT, IDTX} for the 32-point sizes, DCT_DCT for the 64-point sizes
+        static const uint16_t kSetA[19] = { 0x0E0F, 0xAE0F, 0x0E0F, 0x0201, 0x0001, 0x0E0F, 0x0E0F, 0xAE0F,
+                                            0x5E0F, 0x0201, 0x0201, 0x0001, 0x0001, 0x0E0F, 0x0E0F, 0x0201,
+                                            0x0201, 0x0001, 0x0001 };
+        set &= kSetA[tx_size];
+    }
+    return set ? set : DCTONLY;
+}
+
+// One candidate per (block, tried type): a copy of the block with that tx_type, its own output
+// slot (`cand` index = eob / dist slot) and, when coefficients are wanted, its own coefficient
+// range.  cand must hold 16 * n entries.  Returns the candidate count.
+inline int tx_search_expand(const SvtGpuBlock* blocks, int n, int is_inter, int reduced_tx_set_used,
+                            int tx_search_reduced_set, int want_coeff, SvtGpuBlock* cand,
+                            int32_t* cand_block, int64_t* coeff_elems) {
+    int k = 0;
+    int64_t co = 0;
+    for (int i = 0; i < n; ++i) {
+        const uint32_t m = tx_search_mask(blocks[i].tx_size, is_inter, reduced_tx_set_used, tx_search_reduced_set);
+        for (int t = 0; t < 16; ++t) {
+            if (!((m >> t) & 1)) continue;
+            cand[k] = blocks[i];
+            cand[k].tx_type = uint8_t(t);
+            cand[k].coeff_off = want_coeff ? uint32_t(co) : 0;
+            if (want_coeff) co += max_eob(blocks[i].tx_size);
+            if (cand_block) cand_block[k] = i;
+            ++k;
+        }
+    }
+    if (coeff_elems) *coeff_elems = co;
+    return k;
+}
+
 // Scan order of the coded region (kw x kh, 64-point sizes use their 32-wide counterpart), as a
 // rule instead of the reference's literal tables (EbTransforms.h:331-3348, selected by
 // av1_scan_orders :3349): class 1 "mrow" is raster order, class 2 "mcol" is column-major, class 0

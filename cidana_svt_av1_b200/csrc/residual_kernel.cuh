@@ -137,14 +137,25 @@ SVT_HD constexpr int tx_id(int w, int h) {  // TxSize enum, EbDefinitions.h
 //   stage int16 [NB][H][W]     residual staged by 128-bit coalesced copies (cp.async); after the
 //                              forward column pass the same bytes hold the prediction block and
 //                              then the reconstruction (pixels), copied back out 128 bits at a time
-#ifndef SVT_NT
-#define SVT_NT 256
+#ifndef SVT_R      // experiment knob: tasks per thread and phase for sizes up to 16 points
+#define SVT_R 1
 #endif
 template <int W, int H>
 struct Geo {
     static constexpr int TXS = tx_id(W, H);
-    static constexpr int NT = SVT_NT;                 // threads per CTA
-    static constexpr int NB = NT / cmin(W, H);        // blocks per CTA
+    // threads per CTA: 256 for the three sizes whose buckets fill the GPU many times over and run
+    // fastest that way (16x16 70 vs 73 us, 32x32 51 vs 52, 4x4 equal); 128 elsewhere -- the same
+    // warps per SM in twice as many CTAs fills the small grids better (8x8 55 vs 57 us,
+    // 16x32 14.6 vs 17.0, 32x16 14.1 vs 16.9, 8x16 13.5 vs 14.8, 64x64 25.3 vs 27.2)
+#ifdef SVT_NT_ALL
+    static constexpr int NT = SVT_NT_ALL;
+#else
+    static constexpr int NT = (W == H && (W == 16 || W == 32 || W == 4)) ? 256 : 128;
+#endif
+    // R: how many times a thread runs each phase (on R different blocks).  The phase loops are
+    // rolled, so the 2nd..Rth pass re-uses the instructions the first one fetched.
+    static constexpr int R = cmax(W, H) <= 16 ? SVT_R : 1;
+    static constexpr int NB = R * NT / cmin(W, H);    // blocks per CTA
     static constexpr int LD = W + 4;
     static constexpr int BLK = ((H * LD - W + 31) / 32) * 32 + W;
     static constexpr int KW = cmin(W, 32), KH = cmin(H, 32);  // kept (coded) region
@@ -162,18 +173,19 @@ struct Geo {
     // CTAs with 64 / 80 / 128 registers per thread beat more, register-starved ones (16x16: 69 vs
     // 74 us at 5 CTAs, 8x8: 58 vs 67 us at 8; 32x32: 56 us at 3 vs 60 us at 2)
     static constexpr int CTAS_PER_SM =
-        cmin(cmax(W, H) >= 64 ? 2 : (cmax(W, H) >= 32 ? 3 : (cmax(W, H) >= 16 ? 4 : 5)),
-             cmax(1, (228 * 1024) / (SMEM_BYTES + 6656)));
+        cmin((cmax(W, H) >= 64 ? 2 : (cmax(W, H) >= 32 ? 3 : (cmax(W, H) >= 16 ? 4 : 5))) * 256 / NT,
+             cmax(1, (228 * 1024) / (SMEM_BYTES + 1024 + 104 * NB)));
 };
 
 struct QSet { int zbin, round, quant, qshift, dequant; };  // one of {DC, AC}
 struct QRow { QSet dc, ac; };  // zbin / round already scaled by log_scale
-struct CtaShared {  // small per-CTA state next to the buffers above
-    DevBlock blk[SVT_NT / 4];
-    QRow q[SVT_NT / 4];  // this block's quantizer row, pre-scaled
-    int eob[SVT_NT / 4];
-    unsigned long long energy[SVT_NT / 4];
-    unsigned long long dist[SVT_NT / 4][2];  // sum (coeff - dq)^2, sum coeff^2 over the coded region
+template <int NB>
+struct CtaShared {  // small per-CTA state next to the buffers above (104 bytes per block)
+    DevBlock blk[NB];
+    QRow q[NB];  // this block's quantizer row, pre-scaled
+    int eob[NB];
+    unsigned long long energy[NB];
+    unsigned long long dist[NB][2];  // sum (coeff - dq)^2, sum coeff^2 over the coded region
 };
 
 // read-only global load through L1 (LDG.CONSTANT on the device)
@@ -727,7 +739,7 @@ residual_kernel(const __grid_constant__ KParams p, int first_block, int count) {
     extern __shared__ __align__(16) int smem[];
     int* buf = smem;
     int16_t* stage = reinterpret_cast<int16_t*>(smem + G::BUF_WORDS);
-    __shared__ CtaShared sh;
+    __shared__ CtaShared<G::NB> sh;
     const int tid = threadIdx.x;
 #ifdef SVT_TRACE
     long long tr[7];
@@ -749,28 +761,34 @@ residual_kernel(const __grid_constant__ KParams p, int first_block, int count) {
     constexpr bool WP = (W == H) && (W <= 32);
 #endif
     auto sync = [&] { if constexpr (WP) __syncwarp(); else __syncthreads(); };
-    const int own = WP ? tid / W : tid;                       // the block whose state this thread owns
-    const bool mine = WP ? (tid % W == 0) : (tid < G::NB);
+    // per-block state of blocks own0, own0 + OSTEP, ... belongs to this thread (if `mine`)
+    constexpr int OSTEP = WP ? G::NT / W : G::NT;
+    const int own0 = WP ? tid / W : tid;
+    const bool mine = WP ? (tid % W == 0) : true;
     if (mine) {
-        if (own < nb) sh.blk[own] = p.blocks[base + own];
-        sh.eob[own] = 0;
-        sh.energy[own] = 0ull;
-        if constexpr (DIST) sh.dist[own][0] = sh.dist[own][1] = 0ull;
+        for (int own = own0; own < G::NB; own += OSTEP) {
+            if (own < nb) sh.blk[own] = p.blocks[base + own];
+            sh.eob[own] = 0;
+            sh.energy[own] = 0ull;
+            if constexpr (DIST) sh.dist[own][0] = sh.dist[own][1] = 0ull;
+        }
     }
     sync();
     // the quantizer rows depend on the descriptors; they are fetched while the residual rows are
     // already in flight, not before them (one global round trip less on the CTA's critical path)
     auto fetch_qrows = [&] {
-        if ((p.stages & STAGE_QUANT) && mine && own < nb)
-            sh.q[own] = load_qrow<G::LOG_SCALE>(p.qtables + size_t(sh.blk[own].qrow) * 40);
+        if ((p.stages & STAGE_QUANT) && mine)
+            for (int own = own0; own < nb; own += OSTEP)
+                sh.q[own] = load_qrow<G::LOG_SCALE>(p.qtables + size_t(sh.blk[own].qrow) * 40);
     };
     TR();
-    // copy teams: TPB consecutive threads move one block's rows, 16 bytes per thread per step
-    constexpr int TPB = G::NT / G::NB;
-    const int tb = tid / TPB, tl = tid - tb * TPB;
-    int16_t* my_stage = stage + tb * G::SP;
+    // copy teams: TPB consecutive threads move one block's rows, 16 bytes per thread per step;
+    // a team serves blocks tb0, tb0 + NTEAM, ... (the same blocks its threads transform)
+    constexpr int TPB = cmin(W, H), NTEAM = G::NT / TPB;
+    const int tb0 = tid / TPB, tl = tid - tb0 * TPB;
     if (p.stages & STAGE_FWD) {
-        if (tb < nb) stage_residual<W, H, TPB>(p, sh.blk[tb], my_stage, tl);
+#pragma unroll 1
+        for (int tb = tb0; tb < nb; tb += NTEAM) stage_residual<W, H, TPB>(p, sh.blk[tb], stage + tb * G::SP, tl);
         fetch_qrows();
         g2s_commit_wait();
         sync();
@@ -788,7 +806,10 @@ residual_kernel(const __grid_constant__ KParams p, int first_block, int count) {
     }
     // the residual is consumed: the prediction block streams into the same bytes while the row
     // phase runs
-    if ((p.stages & STAGE_INV) && tb < nb) stage_pred<W, H, TPB>(p, sh.blk[tb], my_stage, tl);
+    if (p.stages & STAGE_INV) {
+#pragma unroll 1
+        for (int tb = tb0; tb < nb; tb += NTEAM) stage_pred<W, H, TPB>(p, sh.blk[tb], stage + tb * G::SP, tl);
+    }
 #pragma unroll 1
     for (int task = tid; task < G::NB * H; task += G::NT) {
         const int b = task / H, r = task % H;
@@ -810,12 +831,14 @@ residual_kernel(const __grid_constant__ KParams p, int first_block, int count) {
     g2s_commit_wait();
     sync();
     TR();
-    if (mine && own < nb) {
-        if (p.stages & STAGE_QUANT) p.eob[sh.blk[own].id] = uint16_t(sh.eob[own]);
-        if ((p.stages & STAGE_FWD) && p.energy) p.energy[sh.blk[own].id] = sh.energy[own];
-        if constexpr (DIST)
-            finish_dist<G::LOG_SCALE>(sh.dist[own][0], sh.dist[own][1], sh.eob[own], sh.energy[own],
-                                      p.dist + 2 * size_t(sh.blk[own].id));
+    if (mine) {
+        for (int own = own0; own < nb; own += OSTEP) {
+            if (p.stages & STAGE_QUANT) p.eob[sh.blk[own].id] = uint16_t(sh.eob[own]);
+            if ((p.stages & STAGE_FWD) && p.energy) p.energy[sh.blk[own].id] = sh.energy[own];
+            if constexpr (DIST)
+                finish_dist<G::LOG_SCALE>(sh.dist[own][0], sh.dist[own][1], sh.eob[own], sh.energy[own],
+                                          p.dist + 2 * size_t(sh.blk[own].id));
+        }
     }
     if (p.stages & STAGE_INV) {
 #pragma unroll 1
@@ -825,7 +848,8 @@ residual_kernel(const __grid_constant__ KParams p, int first_block, int count) {
         }
         sync();
         TR();
-        if (tb < nb) unstage_recon<W, H, TPB>(p, sh.blk[tb], my_stage, tl);
+#pragma unroll 1
+        for (int tb = tb0; tb < nb; tb += NTEAM) unstage_recon<W, H, TPB>(p, sh.blk[tb], stage + tb * G::SP, tl);
         TR();
     }
 #ifdef SVT_TRACE

@@ -235,6 +235,18 @@ int svtgpu_run_internal(SvtGpuContext* c, const SvtGpuPlan* pl, const SvtGpuBuff
     return SVTGPU_OK;
 }
 
+extern "C" uint32_t svtgpu_tx_search_mask(int tx_size, int is_inter, int reduced_tx_set_used,
+                                          int tx_search_reduced_set) {
+    return tx_search_mask(tx_size, is_inter, reduced_tx_set_used, tx_search_reduced_set);
+}
+extern "C" int svtgpu_tx_search_expand(const SvtGpuBlock* blocks, int n_blocks, int is_inter,
+                                       int reduced_tx_set_used, int tx_search_reduced_set, int want_coeff,
+                                       SvtGpuBlock* cand, int32_t* cand_block, int64_t* coeff_elems) {
+    if (n_blocks < 0 || (n_blocks && (!blocks || !cand))) return SVTGPU_ERR_ARG;
+    return tx_search_expand(blocks, n_blocks, is_inter, reduced_tx_set_used, tx_search_reduced_set,
+                            want_coeff, cand, cand_block, coeff_elems);
+}
+
 extern "C" int svtgpu_sync(SvtGpuContext* c) {
     if (!c) return SVTGPU_ERR_ARG;
     CK(cudaSetDevice(c->device));

@@ -108,6 +108,27 @@ long long svtgpu_total_launch_count(void);
 /* diagnostics: buffer (re)allocations made so far by the host pipeline (0 in steady state) */
 long long svtgpu_debug_host_allocs(void);
 
+/* ------------------------------------------------------------------------------------------ */
+/* batched tx-type search (ProductFullLoopTxSearch, EbFullLoop.c:927-1100)          */
+/* ------------------------------------------------------------------------------------------ */
+/* The reference tries the allowed tx types of a block one after another around
+ * av1_estimate_transform -> av1_quantize_inv_quantize -> picture_full_distortion32_bits and keeps
+ * the cheapest.  Here the candidates of a whole block list go through ONE run of the fused path
+ * (STAGE_FWD | STAGE_QUANT [| STAGE_RESIDUAL], `dist` output): the caller gets {eob, distortion
+ * pair} (and optionally qcoeff for its rate estimate) per candidate and applies its own cost.
+ *
+ * svtgpu_tx_search_mask: bit t set = the reference's loop evaluates tx type t for this size
+ * (get_ext_tx_set_type / av1_ext_tx_used, EbDefinitions.h:1472-1500; allowed_tx_set_a,
+ * EbFullLoop.c:883-902 when tx_search_reduced_set).
+ * svtgpu_tx_search_expand: writes one SvtGpuBlock per (block, tried type) into cand[16 * n]
+ * (cand index = eob / dist slot), the owning block index into cand_block, and the total
+ * coefficient elements (0 unless want_coeff).  Returns the candidate count.  Host only. */
+uint32_t svtgpu_tx_search_mask(int tx_size, int is_inter, int reduced_tx_set_used,
+                               int tx_search_reduced_set);
+int svtgpu_tx_search_expand(const SvtGpuBlock *blocks, int n_blocks, int is_inter,
+                            int reduced_tx_set_used, int tx_search_reduced_set, int want_coeff,
+                            SvtGpuBlock *cand, int32_t *cand_block, int64_t *coeff_elems);
+
 /* thin memory helpers so that a C caller needs no CUDA headers */
 int svtgpu_malloc(SvtGpuContext *ctx, void **dev_ptr, size_t bytes);
 int svtgpu_free(SvtGpuContext *ctx, void *dev_ptr);

@@ -328,3 +328,30 @@ void ref_tu_distortion(int32_t *coeff, int32_t *recon_coeff, int tx_size, int eo
     dist[0] = RIGHT_SIGNED_SHIFT(y[DIST_CALC_RESIDUAL], shift);
     dist[1] = RIGHT_SIGNED_SHIFT(y[DIST_CALC_PREDICTION], shift);
 }
+
+/* ---- which tx types ProductFullLoopTxSearch evaluates (Codec/EbFullLoop.c:946-982),
+ * from the reference's own get_ext_tx_set_type / av1_ext_tx_used / txsize_sqr_up_map
+ * (Codec/EbDefinitions.h) and its shortlist table allowed_tx_set_a (Codec/EbFullLoop.c:883) ------ */
+extern uint8_t allowed_tx_set_a[TX_SIZES_ALL][TX_TYPES];
+uint32_t ref_tx_search_mask(int tx_size, int is_inter, int reduced_tx_set_used, int tx_search_reduced_set) {
+    const TxSize txSize = (TxSize)tx_size;
+    const TxSetType tx_set_type = get_ext_tx_set_type(txSize, is_inter, reduced_tx_set_used);
+    int32_t allowed_tx_mask[TX_TYPES] = { 0 };
+    int32_t allowed_tx_num = 0;
+    for (int32_t tx_type_index = DCT_DCT; tx_type_index < TX_TYPES; ++tx_type_index) {
+        TxType tx_type = (TxType)tx_type_index;
+        allowed_tx_mask[tx_type] = 1;
+        const TxType ref_tx_type = ((!av1_ext_tx_used[tx_set_type][tx_type]) ||
+                                    txsize_sqr_up_map[txSize] > TX_32X32) ? DCT_DCT : tx_type;
+        if (tx_type != ref_tx_type) allowed_tx_mask[tx_type] = 0;
+        allowed_tx_num += allowed_tx_mask[tx_type];
+    }
+    if (allowed_tx_num == 0) allowed_tx_mask[DCT_DCT] = 1;
+    uint32_t m = 0;
+    for (int32_t t = 0; t < TX_TYPES; ++t) {
+        if (!allowed_tx_mask[t]) continue;
+        if (tx_search_reduced_set && !allowed_tx_set_a[txSize][t]) continue;
+        m |= 1u << t;
+    }
+    return m;
+}

@@ -628,10 +628,10 @@ void svto_tu_distortion(const int32_t *coeff, const int32_t *recon_coeff, int tx
 /* svto_fused_blocks with the residual taken from source - prediction (src has the geometry of
  * the prediction / reconstruction planes) and the per-block distortion pair. `recon` holds the
  * prediction on entry, like svto_fused_blocks. */
-void svto_fused_blocks_md(const SvtoBlock *blk, int first, int last, const void *src, void *recon,
-                          const int16_t *tables, int32_t *qcoeff, int32_t *dqcoeff, uint16_t *eob,
-                          uint64_t *energy, uint64_t *dist, const int16_t *const *scans,
-                          int clamp16) {
+static void fused_blocks_md(const SvtoBlock *blk, int first, int last, const void *src, void *recon,
+                            const int16_t *tables, int32_t *qcoeff, int32_t *dqcoeff, uint16_t *eob,
+                            uint64_t *energy, uint64_t *dist, const int16_t *const *scans,
+                            int clamp16, int do_inverse) {
     int32_t *coeff = (int32_t *)malloc(sizeof(int32_t) * 4096);
     int16_t *res = (int16_t *)malloc(sizeof(int16_t) * 4096);
     for (int i = first; i < last; ++i) {
@@ -650,7 +650,7 @@ void svto_fused_blocks_md(const SvtoBlock *blk, int first, int last, const void 
                       (clamp16 || (b->flags & 1)) && b->bd == 8);
         svto_tu_distortion(coeff, dqcoeff + b->coeff_off, b->tx_size, eob[i], energy[i],
                            dist + 2 * (size_t)i);
-        if (eob[i]) {
+        if (eob[i] && do_inverse) {
             if (b->bd == 8)
                 svto_inv_txfm2d_add8(dqcoeff + b->coeff_off, (uint8_t *)recon + b->rec_off,
                                      b->rec_stride, b->tx_size, b->tx_type);
@@ -661,4 +661,21 @@ void svto_fused_blocks_md(const SvtoBlock *blk, int first, int last, const void 
     }
     free(coeff);
     free(res);
+}
+void svto_fused_blocks_md(const SvtoBlock *blk, int first, int last, const void *src, void *recon,
+                          const int16_t *tables, int32_t *qcoeff, int32_t *dqcoeff, uint16_t *eob,
+                          uint64_t *energy, uint64_t *dist, const int16_t *const *scans,
+                          int clamp16) {
+    fused_blocks_md(blk, first, last, src, recon, tables, qcoeff, dqcoeff, eob, energy, dist, scans,
+                    clamp16, 1);
+}
+/* one iteration of the tx-type loop of ProductFullLoopTxSearch (EbFullLoop.c:984-1075)
+ * per listed candidate -- transform, quantize, distortion; the prediction is only read, so any
+ * number of candidates may name the same block */
+void svto_tx_search_blocks(const SvtoBlock *blk, int first, int last, const void *src, const void *pred,
+                           const int16_t *tables, int32_t *qcoeff, int32_t *dqcoeff, uint16_t *eob,
+                           uint64_t *energy, uint64_t *dist, const int16_t *const *scans,
+                           int clamp16) {
+    fused_blocks_md(blk, first, last, src, (void *)pred, tables, qcoeff, dqcoeff, eob, energy, dist,
+                    scans, clamp16, 0);
 }

@@ -92,6 +92,11 @@ void svto_fused_blocks_md(const SvtoBlock *blk, int first, int last, const void 
                           const int16_t *tables, int32_t *qcoeff, int32_t *dqcoeff, uint16_t *eob,
                           uint64_t *energy, uint64_t *dist, const int16_t *const *scans,
                           int clamp16);
+/* the same per candidate of a tx-type search: no inverse, `pred` is only read */
+void svto_tx_search_blocks(const SvtoBlock *blk, int first, int last, const void *src, const void *pred,
+                          const int16_t *tables, int32_t *qcoeff, int32_t *dqcoeff, uint16_t *eob,
+                          uint64_t *energy, uint64_t *dist, const int16_t *const *scans,
+                          int clamp16);
 
 #ifdef __cplusplus
 }

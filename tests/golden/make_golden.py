@@ -22,6 +22,13 @@ from oracle_lib import P, TX_H, TX_W, aligned, aligned_copy, max_eob, ref, valid
 def main():
     R = ref(1)
     assert R is not None, "build oracle/_ref first: make -C oracle ref"
+    only = sys.argv[1] if len(sys.argv) > 1 else None
+    if only == "tx_search":  # add this fixture without touching the others
+        R.ref_tx_search_mask.restype = ctypes.c_uint32
+        masks = np.array([[[[R.ref_tx_search_mask(s, i, r, a) for a in (0, 1)] for r in (0, 1)] for i in (0, 1)]
+                          for s in range(19)], np.uint32)
+        np.savez_compressed(os.path.join(HERE, "tx_search_masks.npz"), masks=masks)
+        return
     # --- quantizer tables
     qt = {}
     for bd in (8, 10):
@@ -85,7 +92,12 @@ def main():
             fv["rec_" + k] = rec
             fv["meta_" + k] = np.array([qi, e.value, en.value & 0xFFFFFFFF, en.value >> 32], np.int64)
     np.savez_compressed(os.path.join(HERE, "fused_vectors.npz"), **fv)
-    for f in ("quant_tables.npz", "scans.npz", "qmatrix.npz", "fused_vectors.npz"):
+    # --- tx types tried by ProductFullLoopTxSearch, [size][inter][reduced set][shortlist]
+    R.ref_tx_search_mask.restype = ctypes.c_uint32
+    masks = np.array([[[[R.ref_tx_search_mask(s, i, r, a) for a in (0, 1)] for r in (0, 1)] for i in (0, 1)]
+                      for s in range(19)], np.uint32)
+    np.savez_compressed(os.path.join(HERE, "tx_search_masks.npz"), masks=masks)
+    for f in ("quant_tables.npz", "scans.npz", "qmatrix.npz", "fused_vectors.npz", "tx_search_masks.npz"):
         print(f, os.path.getsize(os.path.join(HERE, f)))
 
 

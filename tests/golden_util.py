@@ -38,6 +38,12 @@ def load_qmatrices():
     return out
 
 
+def load_tx_search_masks():
+    """uint32[19][2][2][2]: bit t = ProductFullLoopTxSearch tries tx type t, indexed
+    [tx_size][is_inter][reduced_tx_set_used][tx_search_reduced_set] (from the reference build)."""
+    return _npz("tx_search_masks.npz")["masks"]
+
+
 def load_fused_vectors():
     return _npz("fused_vectors.npz")
 

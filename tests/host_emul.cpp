@@ -85,3 +85,10 @@ extern "C" int emul_get_iscan(int tx_size, int cls, int16_t* out) {
     return (int)t.size();
 }
 extern "C" int emul_cospi(int bit, int j) { return kCos.v[bit - 10][j]; }
+extern "C" unsigned emul_tx_search_mask(int s, int inter, int reduced, int shortlist) {
+    return tx_search_mask(s, inter, reduced, shortlist);
+}
+extern "C" int emul_tx_search_expand(const SvtGpuBlock* blocks, int n, int inter, int reduced, int shortlist,
+                                     int want_coeff, SvtGpuBlock* cand, int32_t* cand_block, int64_t* coeff_elems) {
+    return tx_search_expand(blocks, n, inter, reduced, shortlist, want_coeff, cand, cand_block, coeff_elems);
+}

@@ -149,8 +149,9 @@ def run_oracle(batch, tables, scans, clamp16=0, qm=None, threads=1, first=0, las
     return dict(qcoeff=q, dqcoeff=dq, eob=eob, energy=energy, recon=recon)
 
 
-def run_oracle_md(batch, tables, scans, clamp16=0, threads=1):
-    """svto_fused_blocks_md: residual from batch.src - batch.pred, plus the distortion pairs."""
+def run_oracle_md(batch, tables, scans, clamp16=0, threads=1, inverse=True):
+    """svto_fused_blocks_md: residual from batch.src - batch.pred, plus the distortion pairs.
+    inverse=False: svto_tx_search_blocks (candidates of a tx-type search: no reconstruction)."""
     import threading
     O = oracle()
     n = batch.n_blocks
@@ -170,8 +171,9 @@ def run_oracle_md(batch, tables, scans, clamp16=0, threads=1):
     blocks = np.ascontiguousarray(batch.blocks)
 
     def work(a, b):
-        O.svto_fused_blocks_md(P(blocks), a, b, P(batch.src), P(recon), P(tables), P(q), P(dq), P(eob),
-                               P(energy), P(dist), ptrs, int(clamp16))
+        fn = O.svto_fused_blocks_md if inverse else O.svto_tx_search_blocks
+        fn(P(blocks), a, b, P(batch.src), P(recon), P(tables), P(q), P(dq), P(eob),
+           P(energy), P(dist), ptrs, int(clamp16))
     sl = _slices(n, threads)
     th = [threading.Thread(target=work, args=x) for x in sl]
     [t.start() for t in th]
