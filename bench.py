@@ -149,6 +149,65 @@ def reference_arm(args, rank, world):
     return 0
 
 
+def mode_arm(args, local_rank):
+    """--mode md / txsearch (N = 1): the SURVEY 8f rows next to the headline path, device-resident.
+    md       = what mode decision consumes: source + prediction in, eob + distortion pair +
+               reconstruction out, no coefficient arrays (8f-1);
+    txsearch = every block expanded into one candidate per tx type ProductFullLoopTxSearch tries
+               (inter, full set), forward + quantise + distortion per candidate (8f-2)."""
+    import torch
+    import cidana_svt_av1_b200 as pkg
+    from cidana_svt_av1_b200.api import STAGE_ALL, STAGE_FWD, STAGE_QUANT, STAGE_RESIDUAL, tx_search_candidates
+
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    batch = make_batch(args.workload, 0).with_source()
+    g = pkg.SvtGpu(local_rank)
+    g.upload_quant_tables(load_tables(batch.bd))
+    px = 1 if batch.bd == 8 else 2
+    if args.mode == "md":
+        work, stages = batch, STAGE_ALL | STAGE_RESIDUAL
+        nbytes = batch.n_samples * 3 * px + batch.n_blocks * (32 + 2 + 8 + 16)
+        what = "source + prediction in; eob, distortion pair, reconstruction out (no coefficient arrays)"
+    else:
+        work = tx_search_candidates(batch, 1, 0, 0, want_coeff=False)
+        stages = STAGE_FWD | STAGE_QUANT | STAGE_RESIDUAL
+        nbytes = batch.n_samples * 2 * px + work.n_blocks * (32 + 2 + 8 + 16)
+        what = (f"{work.n_blocks} candidates of {batch.n_blocks} blocks (inter, full tx set); forward + quantise + "
+                "distortion per candidate, source and prediction read once per block from HBM")
+    plan = g.plan(work.blocks)
+    st = torch.cuda.Stream(dev)
+    pdt = np.uint8 if batch.bd == 8 else np.int16
+    with torch.cuda.stream(st):
+        d = dict(src=torch.from_numpy(batch.src.view(pdt)).to(dev), pred=torch.from_numpy(batch.pred.view(pdt)).to(dev))
+        d["recon"] = torch.empty_like(d["pred"])
+        d["eob"] = torch.empty(work.n_blocks, dtype=torch.int16, device=dev)
+        d["energy"] = torch.empty(work.n_blocks, dtype=torch.int64, device=dev)
+        d["dist"] = torch.empty(2 * work.n_blocks, dtype=torch.int64, device=dev)
+    st.synchronize()
+    for _ in range(max(args.warmup, 3)):
+        g.run(plan, stages, st.cuda_stream, **d)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    st.synchronize()
+    l0 = g.launches
+    e0.record(st)
+    for _ in range(args.steps):
+        g.run(plan, stages, st.cuda_stream, **d)
+    e1.record(st)
+    st.synchronize()
+    ms = e0.elapsed_time(e1) / args.steps
+    hbm, which = peaks()
+    print(json.dumps({"metric": f"{METRIC} ({args.mode} mode)", "value": work.n_samples / ms / 1e3, "unit": UNIT,
+                      "n_gpus": 1, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms,
+                      "higher_is_better": True, "dtype": "int32", "data": "synthetic",
+                      "config": {"workload": WORKLOADS[args.workload][1], "mode": args.mode, "what": what,
+                                 "samples_per_step": work.n_samples, "blocks_per_step": work.n_blocks},
+                      "roofline": {"bound": "hbm", "achieved": nbytes / ms / 1e6, "peak": hbm, "peak_source": which,
+                                   "unit": "GB/s", "frac": nbytes / ms / 1e6 / hbm, "algorithmic_bytes_per_step": nbytes},
+                      "gpu_launches": g.launches - l0}), flush=True)
+    return 0
+
+
 def gpu_arm(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
@@ -327,6 +386,8 @@ def main():
     ap.add_argument("--workload", default="1080p8", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--per-kernel", action="store_true", help="time every size bucket alone (stderr)")
+    ap.add_argument("--mode", default="fused", choices=["fused", "md", "txsearch"],
+                    help="fused = the headline path; md / txsearch = the SURVEY 8f rows (N = 1, extra lines)")
     ap.add_argument("--kernel-only", action="store_true",
                     help="timed steps only (for ncu): no roofline sub-run, e2e or cpu_baseline")
     args = ap.parse_args()
@@ -335,6 +396,8 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
         return reference_arm(args, rank, world)
+    if args.mode != "fused":
+        return mode_arm(args, local_rank) if rank == 0 else 0
     return gpu_arm(args, rank, world, local_rank)
 
 
