@@ -1,5 +1,5 @@
 // Kernel instantiation + launch, split over several translation units so that they compile in
-// parallel: svt_gpu_kernels_{flat,qm,dist}_{a,b}.cu each instantiate launch_part<QM, DIST, PART>
+// parallel: svt_gpu_kernels_{flat,flatfull,qm,qmfull,dist}_{a,b}.cu each instantiate launch_part<QM, DIST, FULL, PART>
 // for half of the 19 transform sizes; svt_gpu_api.cu only sees launch_bucket().
 #pragma once
 #include <cuda_runtime.h>
@@ -7,27 +7,27 @@
 
 namespace svt {
 
-template <int W, int H, bool QM, bool DIST>
+template <int W, int H, bool QM, bool DIST, bool FULL>
 static cudaError_t launch_size(const KParams& p, int first, int count, cudaStream_t st) {
     using G = Geo<W, H>;
     static bool configured[64] = {};  // per device: opt in to > 48 KB of dynamic shared memory
     int dev = 0;
     cudaGetDevice(&dev);
     if (!configured[dev & 63]) {
-        cudaError_t e = cudaFuncSetAttribute(residual_kernel<W, H, QM, DIST>,
+        cudaError_t e = cudaFuncSetAttribute(residual_kernel<W, H, QM, DIST, FULL>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES);
         if (e != cudaSuccess) return e;
         configured[dev & 63] = true;
     }
     const int grid = (count + G::NB - 1) / G::NB;
-    residual_kernel<W, H, QM, DIST><<<grid, G::NT, G::SMEM_BYTES, st>>>(p, first, count);
+    residual_kernel<W, H, QM, DIST, FULL><<<grid, G::NT, G::SMEM_BYTES, st>>>(p, first, count);
     return cudaGetLastError();
 }
 
 // PART 0: the sizes with a 16-point or shorter longest side that are squares or 2:1; PART 1: the rest
-template <bool QM, bool DIST, int PART>
+template <bool QM, bool DIST, bool FULL, int PART>
 cudaError_t launch_part(int tx_size, const KParams& p, int first, int count, cudaStream_t st) {
-#define CASE(id, w, h) case id: return launch_size<w, h, QM, DIST>(p, first, count, st);
+#define CASE(id, w, h) case id: return launch_size<w, h, QM, DIST, FULL>(p, first, count, st);
     if constexpr (PART == 0) {
         switch (tx_size) {
             CASE(0, 4, 4) CASE(1, 8, 8) CASE(2, 16, 16) CASE(3, 32, 32) CASE(5, 4, 8) CASE(6, 8, 4)
@@ -47,12 +47,14 @@ constexpr bool part_of(int tx_size) {  // 1 for the sizes of PART 1
            tx_size >= 15;
 }
 
-#define SVT_DECLARE_PART(QM, DIST, PART) \
-    extern template cudaError_t launch_part<QM, DIST, PART>(int, const KParams&, int, int, cudaStream_t);
-SVT_DECLARE_PART(false, false, 0) SVT_DECLARE_PART(false, false, 1)
-SVT_DECLARE_PART(true, false, 0) SVT_DECLARE_PART(true, false, 1)
-SVT_DECLARE_PART(false, true, 0) SVT_DECLARE_PART(false, true, 1)
-#define SVT_DEFINE_PART(QM, DIST, PART) \
-    template cudaError_t launch_part<QM, DIST, PART>(int, const KParams&, int, int, cudaStream_t);
+#define SVT_DECLARE_PART(QM, DIST, FULL, PART) \
+    extern template cudaError_t launch_part<QM, DIST, FULL, PART>(int, const KParams&, int, int, cudaStream_t);
+SVT_DECLARE_PART(false, false, false, 0) SVT_DECLARE_PART(false, false, false, 1)
+SVT_DECLARE_PART(false, false, true, 0) SVT_DECLARE_PART(false, false, true, 1)
+SVT_DECLARE_PART(true, false, false, 0) SVT_DECLARE_PART(true, false, false, 1)
+SVT_DECLARE_PART(true, false, true, 0) SVT_DECLARE_PART(true, false, true, 1)
+SVT_DECLARE_PART(false, true, false, 0) SVT_DECLARE_PART(false, true, false, 1)
+#define SVT_DEFINE_PART(QM, DIST, FULL, PART) \
+    template cudaError_t launch_part<QM, DIST, FULL, PART>(int, const KParams&, int, int, cudaStream_t);
 
 }  // namespace svt

@@ -18,6 +18,7 @@
 #pragma once
 #include <stddef.h>
 #include <stdint.h>
+#include <type_traits>
 #include "txfm1d.cuh"
 
 #if !defined(__CUDACC__)  // host emulation build (tests only): the two vector helpers used below
@@ -67,6 +68,27 @@ struct KParams {
     unsigned long long* dist;  // optional [n_blocks][2]: tuFullDistortion, EbFullLoop.c:808-835
     int iscan_off[19][3];   // [tx_size][scan class] -> offset into iscan
     int qm_off[2][19];      // [plane > 0][tx_size] -> offset into qm_wt / qm_iwt
+};
+
+// Switches of a launch, as a policy type.  CfgRuntime reads them from KParams (any stage
+// combination, optional outputs); CfgFull fixes them for the headline call -- all three stages,
+// qcoeff and dqcoeff written, no coefficient output -- so that the ~40 uniform branches a warp
+// would otherwise execute disappear from its instruction stream (16x16: 69.3 -> 64.9 us).
+struct CfgRuntime {
+    SVT_HD static int stg(const KParams& p) { return p.stages; }
+    SVT_HD static bool has_q(const KParams& p) { return p.qcoeff != nullptr; }
+    SVT_HD static bool has_dq(const KParams& p) { return p.dqcoeff != nullptr; }
+    SVT_HD static bool has_cf(const KParams& p) { return p.coeff_out != nullptr; }
+};
+struct CfgFull {
+    SVT_HD static constexpr int stg(const KParams&) { return STAGE_ALL; }
+    SVT_HD static constexpr bool has_q(const KParams&) { return true; }
+    SVT_HD static constexpr bool has_dq(const KParams&) { return true; }
+    SVT_HD static constexpr bool has_cf(const KParams&) { return false; }
+    // the launch-side test for this configuration
+    static bool matches(const KParams& p) {
+        return p.stages == STAGE_ALL && p.qcoeff && p.dqcoeff && !p.coeff_out && !p.dist;
+    }
 };
 
 // ---- per-size constants (reference Source/Lib/Common/Codec/EbTransforms.h:121-156, :268-286) ----
@@ -425,7 +447,7 @@ SVT_HD int quant_qm(int cf, const QSet& q, int wt, int iwt, int& qc, int& dqc) {
 // writing consecutive 16-byte chunks; then the same for the dequantized row.  Only __syncwarp over
 // the lanes of one block is needed: they always run the same code (same block, same tx type).
 // The host build (emulation tests) has one task at a time and stores directly.
-template <int W, int H>
+template <int W, int H, class C = CfgRuntime>
 SVT_HD void emit_q(const KParams& p, int* row, uint32_t cbase, int c0, const int (&qv)[4], const int (&x)[W]) {
 #if defined(__CUDA_ARCH__)
     if constexpr (Geo<W, H>::KW >= 16) {
@@ -435,12 +457,12 @@ SVT_HD void emit_q(const KParams& p, int* row, uint32_t cbase, int c0, const int
 #endif
     {
         // rows of <= 32 bytes: consecutive lanes already write (nearly) consecutive addresses
-        if (p.qcoeff) *reinterpret_cast<int4*>(p.qcoeff + cbase + c0) = make_int4(qv[0], qv[1], qv[2], qv[3]);
-        if (p.dqcoeff)
+        if (C::has_q(p)) *reinterpret_cast<int4*>(p.qcoeff + cbase + c0) = make_int4(qv[0], qv[1], qv[2], qv[3]);
+        if (C::has_dq(p))
             *reinterpret_cast<int4*>(p.dqcoeff + cbase + c0) = make_int4(x[c0], x[c0 + 1], x[c0 + 2], x[c0 + 3]);
     }
 }
-template <int W, int H>
+template <int W, int H, class C = CfgRuntime>
 SVT_HD void flush_q(const KParams& p, const DevBlock& d, int r, int* row, const int (&x)[W]) {
 #if defined(__CUDA_ARCH__)
     using G = Geo<W, H>;
@@ -454,7 +476,7 @@ SVT_HD void flush_q(const KParams& p, const DevBlock& d, int r, int* row, const 
     const int* rows0 = row - li * G::LD;  // first row of the group
     const uint32_t gbase = d.coeff_off + uint32_t(r - li) * KW;
     // either output may be absent (a caller that only wants eob, distortion and reconstruction)
-    if (p.qcoeff) {
+    if (C::has_q(p)) {
         __syncwarp(bmask);
 #pragma unroll
         for (int i = 0; i < CPR; ++i) {
@@ -464,7 +486,7 @@ SVT_HD void flush_q(const KParams& p, const DevBlock& d, int r, int* row, const 
         }
         __syncwarp(bmask);
     }
-    if (p.dqcoeff) {
+    if (C::has_dq(p)) {
 #pragma unroll
         for (int c = 0; c < KW; c += 4)
             *reinterpret_cast<int4*>(row + c) = make_int4(x[c], x[c + 1], x[c + 2], x[c + 3]);
@@ -482,7 +504,7 @@ SVT_HD void flush_q(const KParams& p, const DevBlock& d, int r, int* row, const 
 
 // DIST: also accumulate this row's share of sum (coeff - dq)^2 and sum coeff^2 over the coded
 // region (full_distortion_kernel32_bits, EbPictureOperators.c:283-313) into dsum[0..1].
-template <int W, int H, int KIND, bool QM, bool DIST>
+template <int W, int H, int KIND, bool QM, bool DIST, class C = CfgRuntime>
 SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int* buf, const int16_t* isc,
                   int& eob_max, unsigned long long& energy_sum, unsigned long long (&dsum)[2]) {
     static_assert(!(QM && DIST), "the distortion outputs are built for the flat quantizer only");
@@ -496,7 +518,7 @@ SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int
     energy_sum = 0;
     const uint32_t cbase = d.coeff_off + r * KW;
 
-    if (p.stages & STAGE_FWD) {
+    if (C::stg(p) & STAGE_FWD) {
 #pragma unroll
         for (int c = 0; c < W; c += 4) {
             const int4 v = *reinterpret_cast<const int4*>(row + c);
@@ -515,12 +537,12 @@ SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int
                 if (r >= KH || c >= KW)
                     energy_sum += (unsigned long long)(int64_t(x[c]) * int64_t(x[c]));
         }
-        if (p.stages & STAGE_FWD_FULL) {
+        if (C::stg(p) & STAGE_FWD_FULL) {
 #pragma unroll
             for (int c = 0; c < W; c += 4)
                 *reinterpret_cast<int4*>(p.coeff_out + d.coeff_off + r * W + c) =
                     make_int4(x[c], x[c + 1], x[c + 2], x[c + 3]);
-        } else if (p.coeff_out && r < KH) {
+        } else if (C::has_cf(p) && r < KH) {
 #pragma unroll
             for (int c = 0; c < KW; c += 4)
                 *reinterpret_cast<int4*>(p.coeff_out + cbase + c) =
@@ -534,7 +556,7 @@ SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int
         }
     }
 
-    if ((p.stages & STAGE_QUANT) && r < KH) {
+    if ((C::stg(p) & STAGE_QUANT) && r < KH) {
         const QSet qa = q.ac;                      // registers, not repeated shared loads
         const QSet q0 = r == 0 ? q.dc : qa;        // position 0 of the block is DC
         const int t1max = (d.meta & META_CLAMP16) ? 32767 : 0x7fffffff;
@@ -563,7 +585,7 @@ SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int
                     x[c] = dqc;
                     last = aq != 0 ? c : last;
                 }
-                emit_q<W, H>(p, row, cbase, c0, qv, x);
+                emit_q<W, H, C>(p, row, cbase, c0, qv, x);
             }
         } else if constexpr (QM) {
             const int qmo = p.qm_off[((d.meta >> META_PLANE_SHIFT) & 3) > 0][G::TXS] + r * KW;
@@ -579,14 +601,14 @@ SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int
                     x[c] = dqc;
                     last = aq != 0 ? c : last;
                 }
-                emit_q<W, H>(p, row, cbase, c0, qv, x);
+                emit_q<W, H, C>(p, row, cbase, c0, qv, x);
             }
         }
         eob_max = last >= 0 ? int(ld_ro(isc + r * KW + last)) + 1 : 0;
-        flush_q<W, H>(p, d, r, row, x);
+        flush_q<W, H, C>(p, d, r, row, x);
     }
 
-    if (p.stages & STAGE_INV) {  // inv_txfm2d_add_c row pass, EbTransforms.c:8215-8236
+    if (C::stg(p) & STAGE_INV) {  // inv_txfm2d_add_c row pass, EbTransforms.c:8215-8236
         if (r < KH) {
             const Clamp krow_c(bd10 ? 18 : 16);  // clamp_buf(bd + 8) and the row stage range: 16 / 18
 #pragma unroll
@@ -613,18 +635,18 @@ SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int
         }
     }
 }
-template <int W, int H, bool QM, bool DIST = false>
+template <int W, int H, bool QM, bool DIST = false, class C = CfgRuntime>
 SVT_HD void phase_row(const KParams& p, const DevBlock& d, const QRow& q, int r, int* buf,
                       const int16_t* isc, int& e, unsigned long long& en, unsigned long long (&ds)[2]) {
     const int kind = kind_of(htx_of(d.meta & META_TYPE_MASK));
-    if constexpr (W == 64) row_k<W, H, 0, QM, DIST>(p, d, q, r, buf, isc, e, en, ds);
+    if constexpr (W == 64) row_k<W, H, 0, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds);
     else if constexpr (W == 32) {
-        if (kind == 2) row_k<W, H, 2, QM, DIST>(p, d, q, r, buf, isc, e, en, ds);
-        else row_k<W, H, 0, QM, DIST>(p, d, q, r, buf, isc, e, en, ds);
+        if (kind == 2) row_k<W, H, 2, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds);
+        else row_k<W, H, 0, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds);
     } else {
-        if (kind == 0) row_k<W, H, 0, QM, DIST>(p, d, q, r, buf, isc, e, en, ds);
-        else if (kind == 1) row_k<W, H, 1, QM, DIST>(p, d, q, r, buf, isc, e, en, ds);
-        else row_k<W, H, 2, QM, DIST>(p, d, q, r, buf, isc, e, en, ds);
+        if (kind == 0) row_k<W, H, 0, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds);
+        else if (kind == 1) row_k<W, H, 1, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds);
+        else row_k<W, H, 2, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds);
     }
 }
 // eob rule, three_quad_energy and scaling of the per-TU distortion (EbFullLoop.c:808-835;
@@ -689,9 +711,9 @@ SVT_HD void phase_inv_col(const DevBlock& d, int c, const int* buf, void* pix) {
 // ---- per-block staging steps shared by the kernel and the host emulation ---------------------------
 SVT_HD int px_bytes(const DevBlock& d) { return (d.meta & META_BD10) ? 2 : 1; }
 SVT_HD bool ud_flip(const DevBlock& d) { return vtx_of(d.meta & META_TYPE_MASK) == 2; }
-template <int W, int H, int NTHR>
+template <int W, int H, int NTHR, class C = CfgRuntime>
 SVT_HD void stage_residual(const KParams& p, const DevBlock& d, int16_t* sres, int tid) {
-    if (p.stages & STAGE_RESIDUAL) {
+    if (C::stg(p) & STAGE_RESIDUAL) {
         if (d.meta & META_BD10)
             stage_diff<H, W, NTHR>(sres, static_cast<const uint16_t*>(p.src) + d.rec_off,
                                    static_cast<const uint16_t*>(p.pred) + d.rec_off, d.rec_stride, ud_flip(d), tid);
@@ -732,10 +754,11 @@ SVT_HD const int16_t* block_iscan(const KParams& p, const DevBlock& d) {
 }
 
 #if defined(__CUDACC__)
-template <int W, int H, bool QM, bool DIST>
+template <int W, int H, bool QM, bool DIST, bool FULL>
 __global__ void __launch_bounds__(Geo<W, H>::NT, Geo<W, H>::CTAS_PER_SM)
 residual_kernel(const __grid_constant__ KParams p, int first_block, int count) {
     using G = Geo<W, H>;
+    using C = typename std::conditional<FULL, CfgFull, CfgRuntime>::type;
     extern __shared__ __align__(16) int smem[];
     int* buf = smem;
     int16_t* stage = reinterpret_cast<int16_t*>(smem + G::BUF_WORDS);
@@ -777,7 +800,7 @@ residual_kernel(const __grid_constant__ KParams p, int first_block, int count) {
     // the quantizer rows depend on the descriptors; they are fetched while the residual rows are
     // already in flight, not before them (one global round trip less on the CTA's critical path)
     auto fetch_qrows = [&] {
-        if ((p.stages & STAGE_QUANT) && mine)
+        if ((C::stg(p) & STAGE_QUANT) && mine)
             for (int own = own0; own < nb; own += OSTEP)
                 sh.q[own] = load_qrow<G::LOG_SCALE>(p.qtables + size_t(sh.blk[own].qrow) * 40);
     };
@@ -786,9 +809,9 @@ residual_kernel(const __grid_constant__ KParams p, int first_block, int count) {
     // a team serves blocks tb0, tb0 + NTEAM, ... (the same blocks its threads transform)
     constexpr int TPB = cmin(W, H), NTEAM = G::NT / TPB;
     const int tb0 = tid / TPB, tl = tid - tb0 * TPB;
-    if (p.stages & STAGE_FWD) {
+    if (C::stg(p) & STAGE_FWD) {
 #pragma unroll 1
-        for (int tb = tb0; tb < nb; tb += NTEAM) stage_residual<W, H, TPB>(p, sh.blk[tb], stage + tb * G::SP, tl);
+        for (int tb = tb0; tb < nb; tb += NTEAM) stage_residual<W, H, TPB, C>(p, sh.blk[tb], stage + tb * G::SP, tl);
         fetch_qrows();
         g2s_commit_wait();
         sync();
@@ -800,13 +823,13 @@ residual_kernel(const __grid_constant__ KParams p, int first_block, int count) {
         }
         sync();
         TR();
-    } else if (p.stages & STAGE_QUANT) {
+    } else if (C::stg(p) & STAGE_QUANT) {
         fetch_qrows();
         sync();
     }
     // the residual is consumed: the prediction block streams into the same bytes while the row
     // phase runs
-    if (p.stages & STAGE_INV) {
+    if (C::stg(p) & STAGE_INV) {
 #pragma unroll 1
         for (int tb = tb0; tb < nb; tb += NTEAM) stage_pred<W, H, TPB>(p, sh.blk[tb], stage + tb * G::SP, tl);
     }
@@ -816,7 +839,7 @@ residual_kernel(const __grid_constant__ KParams p, int first_block, int count) {
         if (b < nb) {
             int e;
             unsigned long long en, ds[2];
-            phase_row<W, H, QM, DIST>(p, sh.blk[b], sh.q[b], r, buf + b * G::BLK,
+            phase_row<W, H, QM, DIST, C>(p, sh.blk[b], sh.q[b], r, buf + b * G::BLK,
                                       block_iscan<W, H>(p, sh.blk[b]), e, en, ds);
             if (e) atomicMax(&sh.eob[b], e);
             if (G::KW != W || G::KH != H) { if (en) atomicAdd(&sh.energy[b], en); }
@@ -833,14 +856,14 @@ residual_kernel(const __grid_constant__ KParams p, int first_block, int count) {
     TR();
     if (mine) {
         for (int own = own0; own < nb; own += OSTEP) {
-            if (p.stages & STAGE_QUANT) p.eob[sh.blk[own].id] = uint16_t(sh.eob[own]);
-            if ((p.stages & STAGE_FWD) && p.energy) p.energy[sh.blk[own].id] = sh.energy[own];
+            if (C::stg(p) & STAGE_QUANT) p.eob[sh.blk[own].id] = uint16_t(sh.eob[own]);
+            if ((C::stg(p) & STAGE_FWD) && p.energy) p.energy[sh.blk[own].id] = sh.energy[own];
             if constexpr (DIST)
                 finish_dist<G::LOG_SCALE>(sh.dist[own][0], sh.dist[own][1], sh.eob[own], sh.energy[own],
                                           p.dist + 2 * size_t(sh.blk[own].id));
         }
     }
-    if (p.stages & STAGE_INV) {
+    if (C::stg(p) & STAGE_INV) {
 #pragma unroll 1
         for (int task = tid; task < G::NB * W; task += G::NT) {
             const int b = task / W, c = task % W;
