@@ -129,13 +129,24 @@ inline void build_iscan_tables(std::vector<int16_t>& all, int off[19][3]) {
 }
 
 // Validates the caller's list and buckets it by tx_size.  Inside a size bucket the caller's order is
-// kept in windows of kSortWindow blocks, and each window is stable-sorted by tx_type: warps then
+// kept in windows of 2^sort_window_log2() blocks, and each window is stable-sorted by tx_type: warps then
 // mostly see one type (no divergence between 1-D kinds), while blocks that are neighbours in the
 // frame -- and share 32-byte DRAM sectors of the pixel rows -- are still processed within a few
 // CTAs of each other, so the second half of a sector is an L2 hit, not another DRAM read.
 // Returns 0 or the 1-based index of the first bad block.
-constexpr int kSortWindowLog2 = 12;
-constexpr int kSortWindow = 1 << kSortWindowLog2;
+#include <stdlib.h>
+// tuning knob SVTGPU_SORT_WINDOW_LOG2 (8..24).  Measured on B200, 1080p8, ms per step:
+// 10 -> 0.2605, 12 -> 0.2574, 13 -> 0.2556, 14 -> 0.2524, 16 -> 0.2616, 20 (whole bucket) -> 0.2767:
+// longer runs of one tx type keep the instruction working set small, until neighbouring blocks
+// stop meeting in L2.
+inline int sort_window_log2() {
+    static const int v = [] {
+        const char* e = getenv("SVTGPU_SORT_WINDOW_LOG2");
+        const int x = e ? atoi(e) : 14;
+        return x < 8 ? 8 : (x > 24 ? 24 : x);
+    }();
+    return v;
+}
 struct BucketScratch {  // reused across calls by callers that bucket a picture per submission
     std::vector<uint32_t> ord;
     std::vector<int> pos;
@@ -144,6 +155,7 @@ struct BucketScratch {  // reused across calls by callers that bucket a picture 
 // in three sequential passes over `in`)
 inline int bucket_blocks(const SvtGpuBlock* in, int n, DevBlock* out, int first[19], int count[19],
                          BucketScratch& sc) {
+    const int kSortWindowLog2 = sort_window_log2(), kSortWindow = 1 << kSortWindowLog2;
     uint16_t valid[19];
     for (int s = 0; s < 19; ++s) {
         valid[s] = 0;

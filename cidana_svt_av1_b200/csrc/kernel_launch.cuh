@@ -1,5 +1,5 @@
 // Kernel instantiation + launch, split over several translation units so that they compile in
-// parallel: svt_gpu_kernels_{flat,flatfull,qm,qmfull,dist}_{a,b}.cu each instantiate launch_part<QM, DIST, FULL, PART>
+// parallel: svt_gpu_kernels_{flat,flatfull8,flatfull10,qm,qmfull10,dist}_{a,b}.cu each instantiate launch_part<QM, DIST, FULL, PART>
 // for half of the 19 transform sizes; svt_gpu_api.cu only sees launch_bucket().
 #pragma once
 #include <cuda_runtime.h>
@@ -7,7 +7,7 @@
 
 namespace svt {
 
-template <int W, int H, bool QM, bool DIST, bool FULL>
+template <int W, int H, bool QM, bool DIST, int FULL>
 static cudaError_t launch_size(const KParams& p, int first, int count, cudaStream_t st) {
     using G = Geo<W, H>;
     static bool configured[64] = {};  // per device: opt in to > 48 KB of dynamic shared memory
@@ -25,7 +25,7 @@ static cudaError_t launch_size(const KParams& p, int first, int count, cudaStrea
 }
 
 // PART 0: the sizes with a 16-point or shorter longest side that are squares or 2:1; PART 1: the rest
-template <bool QM, bool DIST, bool FULL, int PART>
+template <bool QM, bool DIST, int FULL, int PART>
 cudaError_t launch_part(int tx_size, const KParams& p, int first, int count, cudaStream_t st) {
 #define CASE(id, w, h) case id: return launch_size<w, h, QM, DIST, FULL>(p, first, count, st);
     if constexpr (PART == 0) {
@@ -49,11 +49,12 @@ constexpr bool part_of(int tx_size) {  // 1 for the sizes of PART 1
 
 #define SVT_DECLARE_PART(QM, DIST, FULL, PART) \
     extern template cudaError_t launch_part<QM, DIST, FULL, PART>(int, const KParams&, int, int, cudaStream_t);
-SVT_DECLARE_PART(false, false, false, 0) SVT_DECLARE_PART(false, false, false, 1)
-SVT_DECLARE_PART(false, false, true, 0) SVT_DECLARE_PART(false, false, true, 1)
-SVT_DECLARE_PART(true, false, false, 0) SVT_DECLARE_PART(true, false, false, 1)
-SVT_DECLARE_PART(true, false, true, 0) SVT_DECLARE_PART(true, false, true, 1)
-SVT_DECLARE_PART(false, true, false, 0) SVT_DECLARE_PART(false, true, false, 1)
+SVT_DECLARE_PART(false, false, 0, 0) SVT_DECLARE_PART(false, false, 0, 1)
+SVT_DECLARE_PART(false, false, 8, 0) SVT_DECLARE_PART(false, false, 8, 1)
+SVT_DECLARE_PART(false, false, 10, 0) SVT_DECLARE_PART(false, false, 10, 1)
+SVT_DECLARE_PART(true, false, 0, 0) SVT_DECLARE_PART(true, false, 0, 1)
+SVT_DECLARE_PART(true, false, 10, 0) SVT_DECLARE_PART(true, false, 10, 1)
+SVT_DECLARE_PART(false, true, 0, 0) SVT_DECLARE_PART(false, true, 0, 1)
 #define SVT_DEFINE_PART(QM, DIST, FULL, PART) \
     template cudaError_t launch_part<QM, DIST, FULL, PART>(int, const KParams&, int, int, cudaStream_t);
 

@@ -66,6 +66,8 @@ struct KParams {
     const uint8_t* qm_iwt;
     const void* src;        // STAGE_RESIDUAL: source pixels, geometry of pred
     unsigned long long* dist;  // optional [n_blocks][2]: tuFullDistortion, EbFullLoop.c:808-835
+    int bd_uniform;         // 8 / 10 when every block of the plan has that bit depth, else 0
+    int any_clamp16;        // some block asks for the 8-bit C quantizer variant (META_CLAMP16)
     int iscan_off[19][3];   // [tx_size][scan class] -> offset into iscan
     int qm_off[2][19];      // [plane > 0][tx_size] -> offset into qm_wt / qm_iwt
 };
@@ -79,15 +81,21 @@ struct CfgRuntime {
     SVT_HD static bool has_q(const KParams& p) { return p.qcoeff != nullptr; }
     SVT_HD static bool has_dq(const KParams& p) { return p.dqcoeff != nullptr; }
     SVT_HD static bool has_cf(const KParams& p) { return p.coeff_out != nullptr; }
+    SVT_HD static bool bd10(const DevBlock& d) { return d.meta & META_BD10; }
+    SVT_HD static bool clamp16(const DevBlock& d) { return d.meta & META_CLAMP16; }
 };
+template <int BD>  // the bit depth every block of the launch has (8 or 10): pixel type compiled in
 struct CfgFull {
     SVT_HD static constexpr int stg(const KParams&) { return STAGE_ALL; }
     SVT_HD static constexpr bool has_q(const KParams&) { return true; }
     SVT_HD static constexpr bool has_dq(const KParams&) { return true; }
     SVT_HD static constexpr bool has_cf(const KParams&) { return false; }
+    SVT_HD static constexpr bool bd10(const DevBlock&) { return BD == 10; }
+    SVT_HD static constexpr bool clamp16(const DevBlock&) { return false; }
     // the launch-side test for this configuration
     static bool matches(const KParams& p) {
-        return p.stages == STAGE_ALL && p.qcoeff && p.dqcoeff && !p.coeff_out && !p.dist;
+        return p.stages == STAGE_ALL && p.qcoeff && p.dqcoeff && !p.coeff_out && !p.dist &&
+               p.bd_uniform == BD && !p.any_clamp16;
     }
 };
 
@@ -511,7 +519,7 @@ SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int
     using G = Geo<W, H>;
     dsum[0] = dsum[1] = 0;
     constexpr int KW = G::KW, KH = G::KH, LS = G::LOG_SCALE;
-    const bool bd10 = d.meta & META_BD10;
+    const bool bd10 = C::bd10(d);
     int* row = buf + r * G::LD;
     int x[W];
     eob_max = 0;
@@ -559,7 +567,7 @@ SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int
     if ((C::stg(p) & STAGE_QUANT) && r < KH) {
         const QSet qa = q.ac;                      // registers, not repeated shared loads
         const QSet q0 = r == 0 ? q.dc : qa;        // position 0 of the block is DC
-        const int t1max = (d.meta & META_CLAMP16) ? 32767 : 0x7fffffff;
+        const int t1max = C::clamp16(d) ? 32767 : 0x7fffffff;
         const bool use_qm = QM && (d.meta & META_USE_QM);
         // eob = 1 + the largest scan index of a non-zero level.  Along a row every AV1 scan order
         // (default diagonal, mrow, mcol; all 19 sizes) visits the columns left to right, i.e.
@@ -688,23 +696,23 @@ SVT_HD void inv_col_k(const DevBlock& d, int c, const int* buf, PIX* pix, int pm
         *q = PIX(px < 0 ? 0 : (px > pmax ? pmax : px));
     }
 }
-template <int W, int H, int KIND>
+template <int W, int H, int KIND, class C = CfgRuntime>
 SVT_HD void inv_col_bd(const DevBlock& d, int c, const int* buf, void* pix) {
-    if (d.meta & META_BD10)
+    if (C::bd10(d))
         inv_col_k<W, H, KIND>(d, c, buf, static_cast<uint16_t*>(pix), 1023, (1 << 17) - 1 + (914 << 3));
     else
         inv_col_k<W, H, KIND>(d, c, buf, static_cast<uint8_t*>(pix), 255, (1 << 15) - 1 + (914 << 1));
 }
-template <int W, int H>
+template <int W, int H, class C = CfgRuntime>
 SVT_HD void phase_inv_col(const DevBlock& d, int c, const int* buf, void* pix) {
     const int kind = kind_of(vtx_of(d.meta & META_TYPE_MASK));
-    if constexpr (H == 64) inv_col_bd<W, H, 0>(d, c, buf, pix);
+    if constexpr (H == 64) inv_col_bd<W, H, 0, C>(d, c, buf, pix);
     else if constexpr (H == 32) {
-        if (kind == 2) inv_col_bd<W, H, 2>(d, c, buf, pix); else inv_col_bd<W, H, 0>(d, c, buf, pix);
+        if (kind == 2) inv_col_bd<W, H, 2, C>(d, c, buf, pix); else inv_col_bd<W, H, 0, C>(d, c, buf, pix);
     } else {
-        if (kind == 0) inv_col_bd<W, H, 0>(d, c, buf, pix);
-        else if (kind == 1) inv_col_bd<W, H, 1>(d, c, buf, pix);
-        else inv_col_bd<W, H, 2>(d, c, buf, pix);
+        if (kind == 0) inv_col_bd<W, H, 0, C>(d, c, buf, pix);
+        else if (kind == 1) inv_col_bd<W, H, 1, C>(d, c, buf, pix);
+        else inv_col_bd<W, H, 2, C>(d, c, buf, pix);
     }
 }
 
@@ -714,7 +722,7 @@ SVT_HD bool ud_flip(const DevBlock& d) { return vtx_of(d.meta & META_TYPE_MASK) 
 template <int W, int H, int NTHR, class C = CfgRuntime>
 SVT_HD void stage_residual(const KParams& p, const DevBlock& d, int16_t* sres, int tid) {
     if (C::stg(p) & STAGE_RESIDUAL) {
-        if (d.meta & META_BD10)
+        if (C::bd10(d))
             stage_diff<H, W, NTHR>(sres, static_cast<const uint16_t*>(p.src) + d.rec_off,
                                    static_cast<const uint16_t*>(p.pred) + d.rec_off, d.rec_stride, ud_flip(d), tid);
         else
@@ -726,20 +734,20 @@ SVT_HD void stage_residual(const KParams& p, const DevBlock& d, int16_t* sres, i
                                      reinterpret_cast<char*>(const_cast<int16_t*>(p.residual + d.res_off)),
                                      size_t(d.res_stride) * 2, ud_flip(d), tid);
 }
-template <int W, int H, int NTHR>
+template <int W, int H, int NTHR, class C = CfgRuntime>
 SVT_HD void stage_pred(const KParams& p, const DevBlock& d, void* spix, int tid) {
     char* s = static_cast<char*>(spix);
     char* g = static_cast<char*>(const_cast<void*>(p.pred));
-    if (d.meta & META_BD10)
+    if (C::bd10(d))
         stage_copy<H, W * 2, NTHR, true>(s, g + size_t(d.rec_off) * 2, size_t(d.rec_stride) * 2, ud_flip(d), tid);
     else
         stage_copy<H, W, NTHR, true>(s, g + size_t(d.rec_off), size_t(d.rec_stride), ud_flip(d), tid);
 }
-template <int W, int H, int NTHR>
+template <int W, int H, int NTHR, class C = CfgRuntime>
 SVT_HD void unstage_recon(const KParams& p, const DevBlock& d, const void* spix, int tid) {
     char* s = static_cast<char*>(const_cast<void*>(spix));
     char* g = static_cast<char*>(p.recon);
-    if (d.meta & META_BD10)
+    if (C::bd10(d))
         stage_copy<H, W * 2, NTHR, false>(s, g + size_t(d.rec_off) * 2, size_t(d.rec_stride) * 2, ud_flip(d), tid);
     else
         stage_copy<H, W, NTHR, false>(s, g + size_t(d.rec_off), size_t(d.rec_stride), ud_flip(d), tid);
@@ -754,11 +762,13 @@ SVT_HD const int16_t* block_iscan(const KParams& p, const DevBlock& d) {
 }
 
 #if defined(__CUDACC__)
-template <int W, int H, bool QM, bool DIST, bool FULL>
+// FULL: 0 = switches read at run time (CfgRuntime); 8 / 10 = the headline call on blocks of that
+// bit depth (CfgFull<8>, CfgFull<10>)
+template <int W, int H, bool QM, bool DIST, int FULL>
 __global__ void __launch_bounds__(Geo<W, H>::NT, Geo<W, H>::CTAS_PER_SM)
 residual_kernel(const __grid_constant__ KParams p, int first_block, int count) {
     using G = Geo<W, H>;
-    using C = typename std::conditional<FULL, CfgFull, CfgRuntime>::type;
+    using C = typename std::conditional<FULL != 0, CfgFull<FULL>, CfgRuntime>::type;
     extern __shared__ __align__(16) int smem[];
     int* buf = smem;
     int16_t* stage = reinterpret_cast<int16_t*>(smem + G::BUF_WORDS);
@@ -831,7 +841,7 @@ residual_kernel(const __grid_constant__ KParams p, int first_block, int count) {
     // phase runs
     if (C::stg(p) & STAGE_INV) {
 #pragma unroll 1
-        for (int tb = tb0; tb < nb; tb += NTEAM) stage_pred<W, H, TPB>(p, sh.blk[tb], stage + tb * G::SP, tl);
+        for (int tb = tb0; tb < nb; tb += NTEAM) stage_pred<W, H, TPB, C>(p, sh.blk[tb], stage + tb * G::SP, tl);
     }
 #pragma unroll 1
     for (int task = tid; task < G::NB * H; task += G::NT) {
@@ -867,12 +877,12 @@ residual_kernel(const __grid_constant__ KParams p, int first_block, int count) {
 #pragma unroll 1
         for (int task = tid; task < G::NB * W; task += G::NT) {
             const int b = task / W, c = task % W;
-            if (b < nb) phase_inv_col<W, H>(sh.blk[b], c, buf + b * G::BLK, stage + b * G::SP);
+            if (b < nb) phase_inv_col<W, H, C>(sh.blk[b], c, buf + b * G::BLK, stage + b * G::SP);
         }
         sync();
         TR();
 #pragma unroll 1
-        for (int tb = tb0; tb < nb; tb += NTEAM) unstage_recon<W, H, TPB>(p, sh.blk[tb], stage + tb * G::SP, tl);
+        for (int tb = tb0; tb < nb; tb += NTEAM) unstage_recon<W, H, TPB, C>(p, sh.blk[tb], stage + tb * G::SP, tl);
         TR();
     }
 #ifdef SVT_TRACE

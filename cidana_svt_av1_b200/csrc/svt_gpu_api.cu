@@ -127,7 +127,13 @@ extern "C" int svtgpu_plan_create(SvtGpuContext* c, const SvtGpuBlock* blocks, i
     uint32_t max_qrow = 0;
     for (int i = 0; i < n; ++i) max_qrow = dev[i].qrow > max_qrow ? dev[i].qrow : max_qrow;
     pl->max_qrow = max_qrow;
-    for (int i = 0; i < n; ++i) pl->uses_qm |= (dev[i].meta & META_USE_QM) != 0;
+    int n10 = 0;
+    for (int i = 0; i < n; ++i) {
+        pl->uses_qm |= (dev[i].meta & META_USE_QM) != 0;
+        n10 += (dev[i].meta & META_BD10) != 0;
+        pl->any_clamp16 |= (dev[i].meta & META_CLAMP16) != 0;
+    }
+    pl->bd_uniform = n10 == 0 ? 8 : (n10 == n ? 10 : 0);
     if (n > 0) {
         if (cudaMalloc(&pl->d_blocks, size_t(n) * sizeof(DevBlock)) != cudaSuccess) { delete pl; CK(cudaGetLastError()); return SVTGPU_ERR_NOMEM; }
         CK(cudaMemcpyAsync(pl->d_blocks, dev.data(), size_t(n) * sizeof(DevBlock), cudaMemcpyHostToDevice, c->stream));
@@ -173,7 +179,7 @@ int svtgpu_run_internal(SvtGpuContext* c, const SvtGpuPlan* pl, const SvtGpuBuff
 
     KParams p;
     memset(&p, 0, sizeof(p));
-    p.blocks = pl->d_blocks; p.n_blocks = pl->n; p.stages = stages;
+    p.blocks = pl->d_blocks; p.n_blocks = pl->n; p.stages = stages; p.bd_uniform = pl->bd_uniform; p.any_clamp16 = pl->any_clamp16;
     p.residual = b->residual; p.pred = b->pred; p.recon = b->recon;
     p.coeff_in = b->coeff_in; p.coeff_out = b->coeff; p.qcoeff = b->qcoeff; p.dqcoeff = b->dqcoeff;
     p.eob = b->eob; p.energy = b->energy;

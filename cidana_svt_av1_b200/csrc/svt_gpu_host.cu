@@ -106,8 +106,10 @@ extern "C" int svtgpu_submit_host(SvtGpuContext* c, const SvtGpuHostFrame* f, in
         if (b.bit_depth != f->bit_depth) return SVTGPU_ERR_ARG;
         plan.max_qrow = b.qrow > plan.max_qrow ? b.qrow : plan.max_qrow;
         plan.uses_qm |= (b.flags & SVTGPU_BLK_USE_QM) != 0;
+        plan.any_clamp16 |= (b.flags & SVTGPU_BLK_CLAMP16) != 0;
     }
     plan.d_blocks = s.d_blocks;
+    plan.bd_uniform = f->bit_depth;  // checked per block above
 
     const size_t px = f->bit_depth == 8 ? 1 : 2;
     if (!diff) TRY(grow(s.d_res, s.cap_res, f->residual_elems, s.st));

@@ -1,5 +1,5 @@
-// residual_kernel<W, H, QM = false, DIST = false, FULL = false> for size group 1 (see kernel_launch.cuh)
+// residual_kernel<W, H, QM = false, DIST = false, FULL = 0> for size group 1 (see kernel_launch.cuh)
 #include "kernel_launch.cuh"
 namespace svt {
-SVT_DEFINE_PART(false, false, false, 1)
+SVT_DEFINE_PART(false, false, 0, 1)
 }  // namespace svt

@@ -4,19 +4,21 @@
 #include "svt_gpu_internal.h"
 
 namespace svt {
-template <bool QM, bool DIST, bool FULL>
+template <bool QM, bool DIST, int FULL>
 static cudaError_t launch_v(int tx_size, const KParams& p, int first, int count, cudaStream_t st) {
     return part_of(tx_size) ? launch_part<QM, DIST, FULL, 1>(tx_size, p, first, count, st)
                             : launch_part<QM, DIST, FULL, 0>(tx_size, p, first, count, st);
 }
 cudaError_t launch_bucket(int tx_size, const KParams& p, int first, int count, cudaStream_t st) {
     // the qmatrix variant carries the 64-bit quantizer; keep it out of the common instruction stream
-    if (p.dist) return launch_v<false, true, false>(tx_size, p, first, count, st);  // flat quantizer only (checked by run)
-    // the headline configuration (all stages, q + dq out) has its switches compiled in (CfgFull)
-    if (CfgFull::matches(p))
-        return p.qm_wt ? launch_v<true, false, true>(tx_size, p, first, count, st)
-                       : launch_v<false, false, true>(tx_size, p, first, count, st);
-    return p.qm_wt ? launch_v<true, false, false>(tx_size, p, first, count, st)
-                   : launch_v<false, false, false>(tx_size, p, first, count, st);
+    if (p.dist) return launch_v<false, true, 0>(tx_size, p, first, count, st);  // flat quantizer only (checked by run)
+    // the headline configuration (all stages, q + dq out, one bit depth) has its switches compiled
+    // in (CfgFull); the qmatrix path exists for 10-bit only
+    if (CfgFull<8>::matches(p) && !p.qm_wt) return launch_v<false, false, 8>(tx_size, p, first, count, st);
+    if (CfgFull<10>::matches(p))
+        return p.qm_wt ? launch_v<true, false, 10>(tx_size, p, first, count, st)
+                       : launch_v<false, false, 10>(tx_size, p, first, count, st);
+    return p.qm_wt ? launch_v<true, false, 0>(tx_size, p, first, count, st)
+                   : launch_v<false, false, 0>(tx_size, p, first, count, st);
 }
 }  // namespace svt
