@@ -1,5 +1,5 @@
 // Kernel instantiation + launch, split over several translation units so that they compile in
-// parallel: svt_gpu_kernels_{flat,flatfull8,flatfull10,qm,qmfull10,dist}_{a,b}.cu each instantiate launch_part<QM, DIST, FULL, PART>
+// parallel: svt_gpu_kernels_{flat,flatfull8,flatfull10,qm,qmfull10,dist,md8,md10,txs8,txs10}_{a,b}.cu each instantiate launch_part<QM, DIST, FULL, PART>
 // for half of the 19 transform sizes; svt_gpu_api.cu only sees launch_bucket().
 #pragma once
 #include <cuda_runtime.h>
@@ -55,6 +55,10 @@ SVT_DECLARE_PART(false, false, 10, 0) SVT_DECLARE_PART(false, false, 10, 1)
 SVT_DECLARE_PART(true, false, 0, 0) SVT_DECLARE_PART(true, false, 0, 1)
 SVT_DECLARE_PART(true, false, 10, 0) SVT_DECLARE_PART(true, false, 10, 1)
 SVT_DECLARE_PART(false, true, 0, 0) SVT_DECLARE_PART(false, true, 0, 1)
+SVT_DECLARE_PART(false, true, 108, 0) SVT_DECLARE_PART(false, true, 108, 1)
+SVT_DECLARE_PART(false, true, 110, 0) SVT_DECLARE_PART(false, true, 110, 1)
+SVT_DECLARE_PART(false, true, 208, 0) SVT_DECLARE_PART(false, true, 208, 1)
+SVT_DECLARE_PART(false, true, 210, 0) SVT_DECLARE_PART(false, true, 210, 1)
 #define SVT_DEFINE_PART(QM, DIST, FULL, PART) \
     template cudaError_t launch_part<QM, DIST, FULL, PART>(int, const KParams&, int, int, cudaStream_t);
 

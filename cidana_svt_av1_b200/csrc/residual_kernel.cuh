@@ -84,18 +84,27 @@ struct CfgRuntime {
     SVT_HD static bool bd10(const DevBlock& d) { return d.meta & META_BD10; }
     SVT_HD static bool clamp16(const DevBlock& d) { return d.meta & META_CLAMP16; }
 };
-template <int BD>  // the bit depth every block of the launch has (8 or 10): pixel type compiled in
+// CFG = 100 * shape + bit depth (8 or 10: the pixel type is compiled in too).  Shapes:
+//   0  headline: forward + quantise + inverse, qcoeff and dqcoeff written
+//   1  mode decision: the same on source - prediction, distortion pair out, no
+//      coefficient arrays
+//   2  tx-type search candidates (8f-2): forward + quantise on source - prediction, distortion
+//      pair out, no coefficient arrays, no reconstruction
+template <int CFG>
 struct CfgFull {
-    SVT_HD static constexpr int stg(const KParams&) { return STAGE_ALL; }
-    SVT_HD static constexpr bool has_q(const KParams&) { return true; }
-    SVT_HD static constexpr bool has_dq(const KParams&) { return true; }
+    static constexpr int BD = CFG % 100, SHAPE = CFG / 100;
+    static constexpr int STAGES = SHAPE == 0 ? STAGE_ALL
+                                : (SHAPE == 1 ? (STAGE_ALL | STAGE_RESIDUAL) : (STAGE_FWD | STAGE_QUANT | STAGE_RESIDUAL));
+    SVT_HD static constexpr int stg(const KParams&) { return STAGES; }
+    SVT_HD static constexpr bool has_q(const KParams&) { return SHAPE == 0; }
+    SVT_HD static constexpr bool has_dq(const KParams&) { return SHAPE == 0; }
     SVT_HD static constexpr bool has_cf(const KParams&) { return false; }
     SVT_HD static constexpr bool bd10(const DevBlock&) { return BD == 10; }
     SVT_HD static constexpr bool clamp16(const DevBlock&) { return false; }
     // the launch-side test for this configuration
     static bool matches(const KParams& p) {
-        return p.stages == STAGE_ALL && p.qcoeff && p.dqcoeff && !p.coeff_out && !p.dist &&
-               p.bd_uniform == BD && !p.any_clamp16;
+        if (p.stages != STAGES || p.coeff_out || p.bd_uniform != BD || p.any_clamp16) return false;
+        return SHAPE == 0 ? (p.qcoeff && p.dqcoeff && !p.dist) : (!p.qcoeff && !p.dqcoeff && p.dist);
     }
 };
 
@@ -600,12 +609,15 @@ SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int
 #pragma unroll
             for (int c0 = 0; c0 < KW; c0 += 4) {
                 int qv[4];
+                // four weights per load (the library keeps every matrix 16-byte aligned)
+                const uint32_t w4 = ld_ro(reinterpret_cast<const uint32_t*>(p.qm_wt + qmo + c0));
+                const uint32_t i4 = ld_ro(reinterpret_cast<const uint32_t*>(p.qm_iwt + qmo + c0));
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     const int c = c0 + j;
                     int dqc;
-                    const int aq = quant_qm<LS>(x[c], c == 0 ? q0 : qa, p.qm_wt[qmo + c],
-                                                p.qm_iwt[qmo + c], qv[j], dqc);
+                    const int aq = quant_qm<LS>(x[c], c == 0 ? q0 : qa, int((w4 >> (8 * j)) & 255),
+                                                int((i4 >> (8 * j)) & 255), qv[j], dqc);
                     x[c] = dqc;
                     last = aq != 0 ? c : last;
                 }
@@ -762,8 +774,7 @@ SVT_HD const int16_t* block_iscan(const KParams& p, const DevBlock& d) {
 }
 
 #if defined(__CUDACC__)
-// FULL: 0 = switches read at run time (CfgRuntime); 8 / 10 = the headline call on blocks of that
-// bit depth (CfgFull<8>, CfgFull<10>)
+// FULL: 0 = switches read at run time (CfgRuntime); otherwise the CFG code of CfgFull
 template <int W, int H, bool QM, bool DIST, int FULL>
 __global__ void __launch_bounds__(Geo<W, H>::NT, Geo<W, H>::CTAS_PER_SM)
 residual_kernel(const __grid_constant__ KParams p, int first_block, int count) {
