@@ -145,7 +145,7 @@ def reference_arm(args, rank, world):
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": runner.kind,
                              "sample": f"each step = one pass over the full batch, {cores} threads"},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
     return 0
 
 
@@ -197,14 +197,14 @@ def mode_arm(args, local_rank):
     st.synchronize()
     ms = e0.elapsed_time(e1) / args.steps
     hbm, which = peaks()
-    print(json.dumps({"metric": f"{METRIC} ({args.mode} mode)", "value": work.n_samples / ms / 1e3, "unit": UNIT,
+    emit({"metric": f"{METRIC} ({args.mode} mode)", "value": work.n_samples / ms / 1e3, "unit": UNIT,
                       "n_gpus": 1, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms,
                       "higher_is_better": True, "dtype": "int32", "data": "synthetic",
                       "config": {"workload": WORKLOADS[args.workload][1], "mode": args.mode, "what": what,
                                  "samples_per_step": work.n_samples, "blocks_per_step": work.n_blocks},
                       "roofline": {"bound": "hbm", "achieved": nbytes / ms / 1e6, "peak": hbm, "peak_source": which,
                                    "unit": "GB/s", "frac": nbytes / ms / 1e6 / hbm, "algorithmic_bytes_per_step": nbytes},
-                      "gpu_launches": g.launches - l0}), flush=True)
+                      "gpu_launches": g.launches - l0})
     return 0
 
 
@@ -276,8 +276,8 @@ def gpu_arm(args, rank, world, local_rank):
 
     if args.kernel_only:
         if rank == 0:
-            print(json.dumps({"metric": METRIC, "value": value, "unit": UNIT, "ms_per_step": ms / args.steps,
-                              "gpu_launches": launches, "kernel_only": True}), flush=True)
+            emit({"metric": METRIC, "value": value, "unit": UNIT, "ms_per_step": ms / args.steps,
+                  "gpu_launches": launches, "kernel_only": True})
         return 0
 
     # ---- roofline of the dominant kernel, timed alone on the launching stream --------------------
@@ -371,10 +371,32 @@ def gpu_arm(args, rank, world, local_rank):
                 "roofline": roof, "cpu_baseline": cpu, "clocks": clocks, "gpu_launches": launches,
                 "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                         "d2h_bytes_per_step": int(d2h), "steps": e2e_steps}}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
+
+
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """Libraries (NCCL's version banner, for one) write to fd 1; the contract is ONE JSON line on
+    stdout.  Everything but emit() goes to stderr from here on."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
 
 
 def main():
@@ -394,6 +416,7 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    quiet_stdout()
     if args.impl == "reference":
         return reference_arm(args, rank, world)
     if args.mode != "fused":

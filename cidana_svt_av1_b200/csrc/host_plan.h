@@ -189,10 +189,8 @@ inline int bucket_blocks(const SvtGpuBlock* in, int n, DevBlock* out, int first[
         d.res_off = b.res_off; d.res_stride = b.res_stride;
         d.rec_off = b.rec_off; d.rec_stride = b.rec_stride;
         d.coeff_off = b.coeff_off; d.qrow = b.qrow; d.id = uint32_t(i);
-        d.meta = uint32_t(b.tx_type) | (b.bit_depth == 10 ? META_BD10 : 0u) |
-                 (uint32_t(b.plane) << META_PLANE_SHIFT) |
-                 ((b.flags & SVTGPU_BLK_CLAMP16) ? META_CLAMP16 : 0u) |
-                 ((b.flags & SVTGPU_BLK_USE_QM) ? META_USE_QM : 0u);
+        d.meta = make_meta(b.tx_type, b.bit_depth, b.plane, b.flags & SVTGPU_BLK_CLAMP16,
+                           b.flags & SVTGPU_BLK_USE_QM);
         out[pos[key0[b.tx_size] + int(ord[i] >> kSortWindowLog2) * 16 + b.tx_type]++] = d;
     }
     return 0;

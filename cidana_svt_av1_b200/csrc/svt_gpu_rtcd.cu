@@ -104,7 +104,7 @@ void run_one(Tls& t, int s, int tx_type, int bd, int stages, bool clamp16) {
     DevBlock& d = *t.h_blk;
     d.res_off = 0; d.res_stride = kTxW[s]; d.rec_off = 0; d.rec_stride = kTxW[s];
     d.coeff_off = 0; d.qrow = 0; d.id = 0;
-    d.meta = uint32_t(tx_type) | (bd == 10 ? META_BD10 : 0u) | (clamp16 ? META_CLAMP16 : 0u);
+    d.meta = make_meta(tx_type, bd, 0, clamp16, false);
     cudaStream_t st = t.ctx->stream;
     CKA(cudaMemcpyAsync(t.plan.d_blocks, t.h_blk, sizeof(DevBlock), cudaMemcpyHostToDevice, st));
     SvtGpuBuffers b;
