@@ -87,6 +87,7 @@ struct CfgRuntime {
     SVT_HD static bool has_cf(const KParams& p) { return p.coeff_out != nullptr; }
     SVT_HD static bool bd10(const DevBlock& d) { return d.meta & META_BD10; }
     SVT_HD static bool clamp16(const DevBlock& d) { return d.meta & META_CLAMP16; }
+    static constexpr int BD_STATIC = 0;  // bit depth not known at compile time
 };
 // CFG = 100 * shape + bit depth (8 or 10: the pixel type is compiled in too).  Shapes:
 //   0  headline: forward + quantise + inverse, qcoeff and dqcoeff written
@@ -96,7 +97,7 @@ struct CfgRuntime {
 //      pair out, no coefficient arrays, no reconstruction
 template <int CFG>
 struct CfgFull {
-    static constexpr int BD = CFG % 100, SHAPE = CFG / 100;
+    static constexpr int BD = CFG % 100, SHAPE = CFG / 100, BD_STATIC = BD;
     static constexpr int STAGES = SHAPE == 0 ? STAGE_ALL
                                 : (SHAPE == 1 ? (STAGE_ALL | STAGE_RESIDUAL) : (STAGE_FWD | STAGE_QUANT | STAGE_RESIDUAL));
     SVT_HD static constexpr int stg(const KParams&) { return STAGES; }
@@ -656,11 +657,20 @@ SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int
             }
             inv1d_k<W, KIND>(x, krow_c);
             constexpr int IS0 = inv_shift0(W, H);
+            // clamp_buf(max(bd + 6, 16)) = 16 bits at the input of the column pass
+            // (EbTransforms.c:8241) is applied here, before the transposing store.  With 8-bit
+            // blocks it cannot bind after a DCT row (its last stage is a 16-bit clamped add/sub and
+            // round_shift only shrinks) nor after an 8/16-point ADST row followed by a shift (the
+            // sign permutation can turn -2^15 into 2^15, which the shift halves), so it is elided
+            // where the bit depth is a compile-time 8.
+            constexpr bool IN_RANGE = C::BD_STATIC == 8 && (KIND == 0 || (KIND == 1 && W >= 8 && IS0 > 0));
+            const Clamp k16(16);
 #pragma unroll
             for (int c = 0; c < W; c += 4) {
-                if constexpr (IS0 > 0) {
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) x[c + j] = rshift<(IS0 > 0 ? IS0 : 1)>(x[c + j]);
+                for (int j = 0; j < 4; ++j) {
+                    if constexpr (IS0 > 0) x[c + j] = rshift<(IS0 > 0 ? IS0 : 1)>(x[c + j]);
+                    if constexpr (!IN_RANGE) x[c + j] = k16(x[c + j]);
                 }
                 *reinterpret_cast<int4*>(row + c) = make_int4(x[c], x[c + 1], x[c + 2], x[c + 3]);
             }
@@ -705,10 +715,10 @@ SVT_HD void inv_col_k(const DevBlock& d, int c, const int* buf, PIX* pix, int pm
     using G = Geo<W, H>;
     const bool lr = d.meta & META_LR;
     const int* src = buf + (lr ? W - 1 - c : c);
-    const Clamp k16(16);  // clamp_buf(max(bd + 6, 16)) and the column stage range: 16 for bd 8 / 10
+    const Clamp k16(16);  // the column stage range: 16 bits for bd 8 / 10
     int x[H];
 #pragma unroll
-    for (int r = 0; r < H; ++r) x[r] = k16(src[r * G::LD]);
+    for (int r = 0; r < H; ++r) x[r] = src[r * G::LD];  // already clamped to 16 bits by the row pass
     inv1d_k<H, KIND>(x, k16);
     // check_range (EbTransforms.c:7794) clamps the residual to +-(2^(7+bd) - 1 + (914 << (bd-7))),
     // i.e. beyond +-34595.  It can never bind here: every 1-D inverse output is bounded by its

@@ -6,7 +6,7 @@
 #include <vector>
 using namespace svt;
 
-template <int W, int H>
+template <int W, int H, class C = CfgRuntime>
 static void run_size(const KParams& p, int first, int count) {
     using G = Geo<W, H>;
     std::vector<int> buf(G::BLK);
@@ -14,10 +14,10 @@ static void run_size(const KParams& p, int first, int count) {
     for (int i = first; i < first + count; ++i) {
         const DevBlock& d = p.blocks[i];
         if (p.stages & STAGE_FWD) {
-            stage_residual<W, H, 1>(p, d, stage, 0);
+            stage_residual<W, H, 1, C>(p, d, stage, 0);
             for (int c = 0; c < W; ++c) phase_fwd_col<W, H>(d, c, buf.data(), stage);
         }
-        if (p.stages & STAGE_INV) stage_pred<W, H, 1>(p, d, stage, 0);
+        if (p.stages & STAGE_INV) stage_pred<W, H, 1, C>(p, d, stage, 0);
         int eob = 0;
         unsigned long long energy = 0;
         QRow q = {};
@@ -26,9 +26,9 @@ static void run_size(const KParams& p, int first, int count) {
         for (int r = 0; r < H; ++r) {
             int e; unsigned long long en, ds[2];
             const int16_t* isc_b = block_iscan<W, H>(p, d);
-            if (p.dist) phase_row<W, H, false, true>(p, d, q, r, buf.data(), isc_b, e, en, ds);
-            else if (p.qm_wt) phase_row<W, H, true, false>(p, d, q, r, buf.data(), isc_b, e, en, ds);
-            else phase_row<W, H, false, false>(p, d, q, r, buf.data(), isc_b, e, en, ds);
+            if (p.dist) phase_row<W, H, false, true, C>(p, d, q, r, buf.data(), isc_b, e, en, ds);
+            else if (p.qm_wt) phase_row<W, H, true, false, C>(p, d, q, r, buf.data(), isc_b, e, en, ds);
+            else phase_row<W, H, false, false, C>(p, d, q, r, buf.data(), isc_b, e, en, ds);
             eob = e > eob ? e : eob;
             energy += en;
             dist[0] += ds[0];
@@ -38,15 +38,25 @@ static void run_size(const KParams& p, int first, int count) {
         if (p.stages & STAGE_QUANT) p.eob[d.id] = (uint16_t)eob;
         if ((p.stages & STAGE_FWD) && p.energy) p.energy[d.id] = energy;
         if (p.stages & STAGE_INV) {
-            for (int c = 0; c < W; ++c) phase_inv_col<W, H>(d, c, buf.data(), stage);
-            unstage_recon<W, H, 1>(p, d, stage, 0);
+            for (int c = 0; c < W; ++c) phase_inv_col<W, H, C>(d, c, buf.data(), stage);
+            unstage_recon<W, H, 1, C>(p, d, stage, 0);
         }
     }
 }
 
+// The compiled-in headline configuration (CfgFull<8> / <10>) when the launch qualifies for it,
+// exactly as svt_gpu_launch.cu selects it; `allow_full` = 0 keeps the run-time switches.
+template <int W, int H>
+static void run_size_cfg(const KParams& p, int first, int count, int allow_full) {
+    if (allow_full && !p.qm_wt && CfgFull<8>::matches(p)) run_size<W, H, CfgFull<8>>(p, first, count);
+    else if (allow_full && CfgFull<10>::matches(p)) run_size<W, H, CfgFull<10>>(p, first, count);
+    else run_size<W, H>(p, first, count);
+}
+static int g_allow_full = 0;
+extern "C" void emul_allow_full(int on) { g_allow_full = on; }
 static int run_bucket(const KParams& p, int tx_size, int first, int count) {
     switch (tx_size) {
-#define CASE(id, w, h) case id: run_size<w, h>(p, first, count); return 0;
+#define CASE(id, w, h) case id: run_size_cfg<w, h>(p, first, count, g_allow_full); return 0;
         CASE(0, 4, 4) CASE(1, 8, 8) CASE(2, 16, 16) CASE(3, 32, 32) CASE(4, 64, 64)
         CASE(5, 4, 8) CASE(6, 8, 4) CASE(7, 8, 16) CASE(8, 16, 8) CASE(9, 16, 32)
         CASE(10, 32, 16) CASE(11, 32, 64) CASE(12, 64, 32) CASE(13, 4, 16) CASE(14, 16, 4)
@@ -68,6 +78,12 @@ extern "C" int emul_run_batch(const SvtGpuBlock* blocks, int n, const SvtGpuBuff
     KParams p = {};
     build_iscan_tables(iscan, p.iscan_off);
     p.blocks = dev.data(); p.n_blocks = n; p.stages = stages;
+    int n10 = 0;
+    for (int i = 0; i < n; ++i) {
+        n10 += blocks[i].bit_depth == 10;
+        p.any_clamp16 |= (blocks[i].flags & SVTGPU_BLK_CLAMP16) != 0;
+    }
+    p.bd_uniform = n10 == 0 ? 8 : (n10 == n ? 10 : 0);
     p.residual = bufs->residual; p.pred = bufs->pred; p.recon = bufs->recon;
     p.coeff_in = bufs->coeff_in; p.coeff_out = bufs->coeff; p.qcoeff = bufs->qcoeff;
     p.dqcoeff = bufs->dqcoeff; p.eob = bufs->eob; p.energy = bufs->energy;

@@ -136,6 +136,38 @@ def test_golden_vectors_from_reference_build():
                     assert np.array_equal(out["coeff"][co:co + n], g["coeff_" + k]), (name, k)
 
 
+@pytest.mark.parametrize("bd", [8, 10])
+def test_compiled_in_headline_configuration(bd):
+    """The headline call runs with its switches compiled in (CfgFull<8> / <10>): stage flags, output
+    pointers, pixel type, no clamp16 -- and, for 8-bit, without the 16-bit clamp at the column
+    input after DCT / long ADST rows, where it cannot bind.  Same arithmetic, checked here on
+    random full-range blocks and on patterns that drive the transforms to their extremes
+    (constant +-max, checkerboards, single rows / columns, alternating stripes)."""
+    E = emul()
+    tables, scans = _tables(bd), load_scans()
+    m = (1 << bd) - 1
+    batches = [wl.make_packed_batch(wl.valid_pairs(), bd, 2, seed=91 + bd, qindex=(0, 40, 255))]
+    ext = wl.make_packed_batch(wl.valid_pairs(), bd, 8, seed=92 + bd, qindex=(0, 10))
+    for i, b in enumerate(ext.blocks):
+        w, h = int(wl.TX_W[b["tx_size"]]), int(wl.TX_H[b["tx_size"]])
+        yy, xx = np.mgrid[0:h, 0:w]
+        pat = [np.full((h, w), m), np.full((h, w), -m), np.where((yy + xx) & 1, m, -m), np.where(yy & 1, m, -m),
+               np.where(xx & 1, -m, m), np.where(yy == 0, m, -m), np.where(xx == w - 1, -m, m),
+               np.where((yy // 2 + xx // 2) & 1, m, -m)][i % 8]
+        o = int(b["res_off"])
+        ext.residual[o:o + w * h] = pat.astype(np.int16).ravel()
+        ext.pred[int(b["rec_off"]):int(b["rec_off"]) + w * h] = (0 if i % 2 else m)
+    batches.append(ext)
+    for k, batch in enumerate(batches):
+        want = run_oracle(batch, tables, scans)
+        E.emul_allow_full(1)
+        try:
+            got = run_emul(batch, tables)
+        finally:
+            E.emul_allow_full(0)
+        _check(got, want, f"compiled-in bd{bd} batch {k}")
+
+
 def test_frame_batch_small():
     batch = wl.make_frame_batch(256, 128, 1, 8, seed=20240)
     tables = _tables(8)
