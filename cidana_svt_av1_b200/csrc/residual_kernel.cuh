@@ -370,11 +370,19 @@ SVT_HD void stage_diff(int16_t* s, const PIX* src, const PIX* prd, size_t gstrid
 
 // ---- 1-D dispatch with the kind as a template argument ----------------------------------------------
 // Each variant contains its own loads and stores, so the three kinds never merge register state.
-template <int N, int BIT, int KIND>
+// POST: round_shift(., POST) of the outputs (av1_round_shift_array_c), folded into the last
+// butterfly stage for DCT / ADST (txfm1d.cuh: hbp) and applied separately after the identity
+template <int N, int BIT, int KIND, int POST = 0>
 SVT_HD void fwd1d_k(int (&x)[N]) {
-    if constexpr (KIND == 0) fdct<N, BIT>(x);
-    else if constexpr (KIND == 1) fadst<N, BIT>(x);
-    else identity<N>(x);
+    if constexpr (KIND == 0) fdct<N, BIT, POST>(x);
+    else if constexpr (KIND == 1) fadst<N, BIT, POST>(x);
+    else {
+        identity<N>(x);
+        if constexpr (POST > 0) {
+#pragma unroll
+            for (int i = 0; i < N; ++i) x[i] = rshift<(POST > 0 ? POST : 1)>(x[i]);
+        }
+    }
 }
 template <int N, int KIND, class K>
 SVT_HD void inv1d_k(int (&x)[N], K k) {
@@ -392,13 +400,10 @@ SVT_HD void fwd_col_k(const DevBlock& d, int c, int* buf, const int16_t* res) {
     int x[H];
 #pragma unroll
     for (int r = 0; r < H; ++r) x[r] = int(res[r * W + c]) * (1 << S0);  // rows already flipped
-    fwd1d_k<H, fwd_cos_col(W, H), KIND>(x);
+    fwd1d_k<H, fwd_cos_col(W, H), KIND, (S1 > 0 ? S1 : 0)>(x);  // includes round_shift(., -shift[1])
     int* dst = buf + (lr ? W - 1 - c : c);  // flip left to right, EbTransforms.c:3752-3757
 #pragma unroll
-    for (int r = 0; r < H; ++r) {
-        if constexpr (S1 > 0) x[r] = rshift<(S1 > 0 ? S1 : 1)>(x[r]);
-        dst[r * G::LD] = x[r];
-    }
+    for (int r = 0; r < H; ++r) dst[r * G::LD] = x[r];
 }
 template <int W, int H>
 SVT_HD void phase_fwd_col(const DevBlock& d, int c, int* buf, const int16_t* res) {
@@ -557,12 +562,11 @@ SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int
             const int4 v = *reinterpret_cast<const int4*>(row + c);
             x[c] = v.x; x[c + 1] = v.y; x[c + 2] = v.z; x[c + 3] = v.w;
         }
-        fwd1d_k<W, fwd_cos_row(W, H), KIND>(x);
         constexpr int S2 = -fwd_shift(W, H, 2);
+        fwd1d_k<W, fwd_cos_row(W, H), KIND, (S2 > 0 ? S2 : 0)>(x);  // includes round_shift(., -shift[2])
+        if constexpr (G::RECT) {
 #pragma unroll
-        for (int c = 0; c < W; ++c) {
-            if constexpr (S2 > 0) x[c] = rshift<(S2 > 0 ? S2 : 1)>(x[c]);
-            if constexpr (G::RECT) x[c] = mul_round12(x[c], 5793);  // EbTransforms.c:3769-3776
+            for (int c = 0; c < W; ++c) x[c] = mul_round12(x[c], 5793);  // EbTransforms.c:3769-3776
         }
         if constexpr (KW != W || KH != H) {  // HandleTransform*_c, EbTransforms.c:4351-4731
 #pragma unroll

@@ -72,6 +72,27 @@ SVT_HD int hb(int w0, int a, int w1, int b) {
 }
 template <int BIT>
 SVT_HD int rshift(int v) { return int(unsigned(v) + (1u << (BIT - 1))) >> BIT; }
+// half_btf followed by round_shift(., POST), as one rounding:
+//   ((z >> BIT) + 2^(POST-1)) >> POST  ==  (z + 2^(BIT+POST-1)) >> (BIT + POST)   (floor of a floor)
+// with z = w0*a + w1*b + 2^(BIT-1).  Exact as long as z + 2^(BIT+POST-1) does not wrap, which legal
+// residuals are far from (|half_btf output| < 2^17 on the forward path, the wrap is at 2^18).
+// Used for the last stage of the forward transforms, whose outputs go straight into the
+// round_shift of av1_round_shift_array_c (EbTransforms.c:3682, :3747, :3768).
+// round_shift(., BIT) followed by round_shift(., POST), as one rounding
+template <int BIT, int POST>
+SVT_HD int rshift2(int v) {
+    if constexpr (POST == 0) return rshift<BIT>(v);
+    else return int(unsigned(v) + ((1u << (BIT - 1)) + (1u << (BIT + POST - 1)))) >> (BIT + POST);
+}
+template <int BIT, int POST>
+SVT_HD int hbp(int w0, int a, int w1, int b) {
+    if constexpr (POST == 0) return hb<BIT>(w0, a, w1, b);
+    else {
+        const unsigned r = unsigned(w0) * unsigned(a) + unsigned(w1) * unsigned(b) +
+                           ((1u << (BIT - 1)) + (1u << (BIT + POST - 1)));
+        return int(r) >> (BIT + POST);
+    }
+}
 
 // Clamp policy: forward transforms do not clamp; inverse transforms clamp every add/sub to the
 // stage range (16 or 18 bits, av1_gen_inv_stage_range EbTransforms.c:5404).
@@ -148,15 +169,15 @@ SVT_HD void mid_rot45(int* y) {  // pi/4 rotation of the middle half of the odd 
         y[q] = hb<BIT>(SVT_C(32), P, SVT_C(32), Q);
     }
 }
-template <int N, int BIT>
+template <int N, int BIT, int POST = 0>
 SVT_HD void end_rot_fwd(int* y) {
     constexpr int M = N / 2;
 #pragma unroll
     for (int i = 0; i < M / 2; ++i) {
         const int b = (64 / N) * (1 + 4 * brev(i, ilog2(M / 2))), a = 64 - b;
         const int lo = y[i], hi = y[M - 1 - i];
-        y[i] = hb<BIT>(SVT_C(a), lo, SVT_C(b), hi);
-        y[M - 1 - i] = hb<BIT>(SVT_C(a), hi, -SVT_C(b), lo);
+        y[i] = hbp<BIT, POST>(SVT_C(a), lo, SVT_C(b), hi);
+        y[M - 1 - i] = hbp<BIT, POST>(SVT_C(a), hi, -SVT_C(b), lo);
     }
 }
 template <int N, int BIT>
@@ -189,19 +210,19 @@ SVT_HD void inv_odd_stages(int* y, K k) {  // W runs 2, 4, ..., M/2
 }
 
 template <int N, int BIT> struct Dct {
-    SVT_HD static void fwd_pos(int* x) {
+    template <int POST = 0> SVT_HD static void fwd_pos(int* x) {
 #pragma unroll
         for (int i = 0; i < N / 2; ++i) {
             const int a = x[i], b = x[N - 1 - i];
             x[i] = a + b;
             x[N - 1 - i] = a - b;
         }
-        Dct<N / 2, BIT>::fwd_pos(x);
+        Dct<N / 2, BIT>::template fwd_pos<POST>(x);
         int* y = x + N / 2;
         constexpr int M = N / 2;
         if constexpr (M >= 4) mid_rot45_fwd(y);
         fwd_odd_stages<M, M / 2, BIT>(y);
-        end_rot_fwd<N, BIT>(y);
+        end_rot_fwd<N, BIT, POST>(y);  // every forward DCT output leaves through a last-stage half_btf
     }
     SVT_HD static void mid_rot45_fwd(int* y) {
         constexpr int M = N / 2;
@@ -229,10 +250,10 @@ template <int N, int BIT> struct Dct {
     }
 };
 template <int BIT> struct Dct<2, BIT> {
-    SVT_HD static void fwd_pos(int* x) {
+    template <int POST = 0> SVT_HD static void fwd_pos(int* x) {
         const int a = x[0], b = x[1];
-        x[0] = hb<BIT>(SVT_C(32), a, SVT_C(32), b);
-        x[1] = hb<BIT>(-SVT_C(32), b, SVT_C(32), a);
+        x[0] = hbp<BIT, POST>(SVT_C(32), a, SVT_C(32), b);
+        x[1] = hbp<BIT, POST>(-SVT_C(32), b, SVT_C(32), a);
     }
     template <class K> SVT_HD static void inv_pos(int* x, K) {
         const int a = x[0], b = x[1];
@@ -241,9 +262,10 @@ template <int BIT> struct Dct<2, BIT> {
     }
 };
 
-template <int N, int BIT>
+// POST: a round_shift(., POST) of every output folded into the last stage (see hbp)
+template <int N, int BIT, int POST = 0>
 SVT_HD void fdct(int (&x)[N]) {
-    Dct<N, BIT>::fwd_pos(x);
+    Dct<N, BIT>::template fwd_pos<POST>(x);
     int t[N];
 #pragma unroll
     for (int k = 0; k < N; ++k) t[k] = x[brev(k, ilog2(N))];
@@ -298,14 +320,14 @@ SVT_HD void adst_bfly(int* x, K k) {
             x[g + i + S] = k.sub(a, b);
         }
 }
-template <int N, int BIT>
+template <int N, int BIT, int POST = 0>
 SVT_HD void adst_last_rot(int* x) {
 #pragma unroll
     for (int i = 0; i < N / 2; ++i) {
         const int u = 32 / N + (128 / N) * i;
         const int a = x[2 * i], b = x[2 * i + 1];
-        x[2 * i] = hb<BIT>(SVT_C(u), a, SVT_C(64 - u), b);
-        x[2 * i + 1] = hb<BIT>(SVT_C(64 - u), a, -SVT_C(u), b);
+        x[2 * i] = hbp<BIT, POST>(SVT_C(u), a, SVT_C(64 - u), b);
+        x[2 * i + 1] = hbp<BIT, POST>(SVT_C(64 - u), a, -SVT_C(u), b);
     }
 }
 template <int N, int GS, int BIT>
@@ -327,7 +349,7 @@ SVT_HD void iadst_stages(int* x, K k) {  // GS runs N, N/2, ..., 4
 
 // ADST4, EbTransforms.c:2764-2854 / :6097-6185 (no clamps; all-zero early-out is a no-op here
 // because the arithmetic maps zeros to zeros)
-template <int BIT>
+template <int BIT, int POST = 0>
 SVT_HD void fadst4(int (&x)[4]) {
     const unsigned s1 = kSin[BIT - 10][1], s2 = kSin[BIT - 10][2], s3 = kSin[BIT - 10][3],
                    s4 = kSin[BIT - 10][4];
@@ -336,10 +358,10 @@ SVT_HD void fadst4(int (&x)[4]) {
     const unsigned a1 = s3 * (x0 + x1 - x3);
     const unsigned a2 = s4 * x0 - s1 * x1 + s2 * x3;
     const unsigned a3 = s3 * x2;
-    x[0] = rshift<BIT>(int(a0 + a3));
-    x[1] = rshift<BIT>(int(a1));
-    x[2] = rshift<BIT>(int(a2 - a3));
-    x[3] = rshift<BIT>(int(a2 - a0 + a3));
+    x[0] = rshift2<BIT, POST>(int(a0 + a3));
+    x[1] = rshift2<BIT, POST>(int(a1));
+    x[2] = rshift2<BIT, POST>(int(a2 - a3));
+    x[3] = rshift2<BIT, POST>(int(a2 - a0 + a3));
 }
 template <int BIT>
 SVT_HD void iadst4(int (&x)[4]) {
@@ -356,10 +378,10 @@ SVT_HD void iadst4(int (&x)[4]) {
     x[3] = rshift<BIT>(int(a0 + a1 - a3));
 }
 
-template <int N, int BIT>
+template <int N, int BIT, int POST = 0>
 SVT_HD void fadst(int (&x)[N]) {
     if constexpr (N == 4) {
-        fadst4<BIT>(x);
+        fadst4<BIT, POST>(x);
     } else {
         int t[N];
 #pragma unroll
@@ -368,7 +390,7 @@ SVT_HD void fadst(int (&x)[N]) {
             t[i] = p < 0 ? -x[-p] : x[p];
         }
         fadst_stages<N, 4, BIT>(t);
-        adst_last_rot<N, BIT>(t);
+        adst_last_rot<N, BIT, POST>(t);
 #pragma unroll
         for (int j = 0; j < N / 2; ++j) {
             x[2 * j] = t[2 * j + 1];
