@@ -15,9 +15,9 @@ static void run_size(const KParams& p, int first, int count) {
         const DevBlock& d = p.blocks[i];
         if (p.stages & STAGE_FWD) {
             stage_residual<W, H, 1, C>(p, d, stage, 0);
-            for (int c = 0; c < W; ++c) phase_fwd_col<W, H>(d, c, buf.data(), stage);
+            for (int c = 0; c < W; ++c) phase_fwd_col<W, H, C::SRC_STAGED>(d, c, buf.data(), stage);
         }
-        if (p.stages & STAGE_INV) stage_pred<W, H, 1, C>(p, d, stage, 0);
+        if ((p.stages & STAGE_INV) && !C::SRC_STAGED) stage_pred<W, H, 1, C>(p, d, stage, 0);
         int eob = 0;
         unsigned long long energy = 0;
         QRow q = {};
@@ -48,7 +48,9 @@ static void run_size(const KParams& p, int first, int count) {
 // exactly as svt_gpu_launch.cu selects it; `allow_full` = 0 keeps the run-time switches.
 template <int W, int H>
 static void run_size_cfg(const KParams& p, int first, int count, int allow_full) {
-    if (allow_full && !p.qm_wt && CfgFull<8>::matches(p)) run_size<W, H, CfgFull<8>>(p, first, count);
+    if (allow_full && p.dist && CfgFull<108>::matches(p)) run_size<W, H, CfgFull<108>>(p, first, count);
+    else if (allow_full && p.dist && CfgFull<208>::matches(p)) run_size<W, H, CfgFull<208>>(p, first, count);
+    else if (allow_full && !p.qm_wt && CfgFull<8>::matches(p)) run_size<W, H, CfgFull<8>>(p, first, count);
     else if (allow_full && CfgFull<10>::matches(p)) run_size<W, H, CfgFull<10>>(p, first, count);
     else run_size<W, H>(p, first, count);
 }

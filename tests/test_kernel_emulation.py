@@ -195,6 +195,19 @@ def test_source_minus_prediction_and_distortion():
             lean = run_emul(batch, tables, stages=7 | 16, dist=True, coeffs=False)
             for k in ("eob", "energy", "recon", "dist"):
                 assert np.array_equal(lean[k], want[k]), k
+            # the same two calls with their switches compiled in (CfgFull<108> / <208> for 8-bit:
+            # source and prediction staged as pixels, the column owner subtracts)
+            E = emul()
+            E.emul_allow_full(1)
+            try:
+                fast = run_emul(batch, tables, stages=7 | 16, dist=True, coeffs=False)
+                cand = run_emul(batch, tables, stages=3 | 16, dist=True, coeffs=False)
+            finally:
+                E.emul_allow_full(0)
+            for k in ("eob", "energy", "recon", "dist"):
+                assert np.array_equal(fast[k], want[k]), ("compiled-in md", k)
+            for k in ("eob", "energy", "dist"):
+                assert np.array_equal(cand[k], want[k]), ("compiled-in tx-search shape", k)
     frame = wl.make_frame_batch(256, 128, 1, 8, seed=7).with_source()
     want = run_oracle_md(frame, _tables(8), scans)
     got = run_emul(frame, _tables(8), stages=7 | 16, dist=True)
