@@ -27,7 +27,8 @@ class SvtGpuError(RuntimeError):
 
 class _Buffers(ctypes.Structure):  # SvtGpuBuffers
     _fields_ = [(n, ctypes.c_void_p) for n in ("residual", "pred", "recon", "coeff_in", "coeff",
-                                               "qcoeff", "dqcoeff", "eob", "energy", "src", "dist")]
+                                               "qcoeff", "dqcoeff", "eob", "energy", "src", "dist",
+                                               "levels", "levels_off")]
 
 
 class _HostFrame(ctypes.Structure):  # SvtGpuHostFrame
@@ -250,6 +251,13 @@ class SvtGpu:
         if own_plan:
             plan.close()
         return out
+
+
+def levels_size(tx_size):
+    """Bytes of one block's padded level map (av1_txb_init_levels layout)."""
+    L = lib()
+    L.svtgpu_levels_size.restype = ctypes.c_size_t
+    return int(L.svtgpu_levels_size(int(tx_size)))
 
 
 def tx_search_mask(tx_size, is_inter=0, reduced_tx_set_used=0, tx_search_reduced_set=0):

@@ -70,6 +70,8 @@ struct KParams {
     const uint8_t* qm_iwt;
     const void* src;        // STAGE_RESIDUAL: source pixels, geometry of pred
     unsigned long long* dist;  // optional [n_blocks][2]: tuFullDistortion, EbFullLoop.c:808-835
+    uint8_t* levels;           // optional padded level maps (av1_txb_init_levels), SURVEY 8f-4
+    const uint32_t* levels_off;  // [n_blocks] byte offset of block id's map
     int bd_uniform;         // 8 / 10 when every block of the plan has that bit depth, else 0
     int any_clamp16;        // some block asks for the 8-bit C quantizer variant (META_CLAMP16)
     int iscan_off[19][3];   // [tx_size][scan class] -> offset into iscan
@@ -85,6 +87,7 @@ struct CfgRuntime {
     SVT_HD static bool has_q(const KParams& p) { return p.qcoeff != nullptr; }
     SVT_HD static bool has_dq(const KParams& p) { return p.dqcoeff != nullptr; }
     SVT_HD static bool has_cf(const KParams& p) { return p.coeff_out != nullptr; }
+    SVT_HD static bool has_lv(const KParams& p) { return p.levels != nullptr; }
     SVT_HD static bool bd10(const DevBlock& d) { return d.meta & META_BD10; }
     SVT_HD static bool clamp16(const DevBlock& d) { return d.meta & META_CLAMP16; }
     static constexpr int BD_STATIC = 0;  // bit depth not known at compile time
@@ -110,11 +113,12 @@ struct CfgFull {
     SVT_HD static constexpr bool has_q(const KParams&) { return SHAPE == 0; }
     SVT_HD static constexpr bool has_dq(const KParams&) { return SHAPE == 0; }
     SVT_HD static constexpr bool has_cf(const KParams&) { return false; }
+    SVT_HD static constexpr bool has_lv(const KParams&) { return false; }
     SVT_HD static constexpr bool bd10(const DevBlock&) { return BD == 10; }
     SVT_HD static constexpr bool clamp16(const DevBlock&) { return false; }
     // the launch-side test for this configuration
     static bool matches(const KParams& p) {
-        if (p.stages != STAGES || p.coeff_out || p.bd_uniform != BD || p.any_clamp16) return false;
+        if (p.stages != STAGES || p.coeff_out || p.levels || p.bd_uniform != BD || p.any_clamp16) return false;
         return SHAPE == 0 ? (p.qcoeff && p.dqcoeff && !p.dist) : (!p.qcoeff && !p.dqcoeff && p.dist);
     }
 };
@@ -618,16 +622,33 @@ SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int
         // the row's candidate is iscan[r][last non-zero column] + 1: one table read per row
         // instead of one per coefficient.
         int last = -1;
+        // this row of the padded level map (av1_txb_init_levels, EbRateDistortionCost.c:125),
+        // its 4 zero bytes of horizontal padding, and this thread's share of the zero rows above
+        // and below the block (2 + 4 rows + 16 bytes = 6 * LP / 4 + 4 words, dealt round robin)
+        uint8_t* lvrow = nullptr;
+        if (C::has_lv(p)) {
+            constexpr int LP = KW + 4;  // pitch of the map
+            uint8_t* base = p.levels + p.levels_off[d.id];
+            lvrow = base + (2 + r) * LP;
+            *reinterpret_cast<uint32_t*>(lvrow + KW) = 0u;
+            constexpr int TOPW = 2 * LP / 4, PADW = TOPW + LP + 4;
+            for (int k = r; k < PADW; k += KH) {
+                uint8_t* q4 = k < TOPW ? base + 4 * k : base + (2 + KH) * LP + 4 * (k - TOPW);
+                *reinterpret_cast<uint32_t*>(q4) = 0u;
+            }
+        }
         if (!use_qm) {
 #pragma unroll
             for (int c0 = 0; c0 < KW; c0 += 4) {
                 int qv[4];
+                uint32_t lv4 = 0;
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     const int c = c0 + j;
                     int dqc;
                     const int cf = x[c];
                     const int aq = quant_flat<LS>(cf, c == 0 ? q0 : qa, t1max, qv[j], dqc);
+                    if (lvrow) lv4 |= uint32_t(aq > 127 ? 127 : aq) << (8 * j);
                     if constexpr (DIST) {
                         const int dd = cf - dqc;
                         dsum[0] += (unsigned long long)((long long)dd * dd);
@@ -636,6 +657,7 @@ SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int
                     x[c] = dqc;
                     last = aq != 0 ? c : last;
                 }
+                if (lvrow) *reinterpret_cast<uint32_t*>(lvrow + c0) = lv4;
                 emit_q<W, H, C>(p, row, cbase, c0, qv, x);
             }
         } else if constexpr (QM) {
@@ -644,6 +666,7 @@ SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int
             for (int c0 = 0; c0 < KW; c0 += 4) {
                 int qv[4];
                 // four weights per load (the library keeps every matrix 16-byte aligned)
+                uint32_t lv4 = 0;
                 const uint32_t w4 = ld_ro(reinterpret_cast<const uint32_t*>(p.qm_wt + qmo + c0));
                 const uint32_t i4 = ld_ro(reinterpret_cast<const uint32_t*>(p.qm_iwt + qmo + c0));
 #pragma unroll
@@ -652,9 +675,11 @@ SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int
                     int dqc;
                     const int aq = quant_qm<LS>(x[c], c == 0 ? q0 : qa, int((w4 >> (8 * j)) & 255),
                                                 int((i4 >> (8 * j)) & 255), qv[j], dqc);
+                    if (lvrow) lv4 |= uint32_t(aq > 127 ? 127 : aq) << (8 * j);
                     x[c] = dqc;
                     last = aq != 0 ? c : last;
                 }
+                if (lvrow) *reinterpret_cast<uint32_t*>(lvrow + c0) = lv4;
                 emit_q<W, H, C>(p, row, cbase, c0, qv, x);
             }
         }

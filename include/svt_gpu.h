@@ -78,7 +78,18 @@ typedef struct SvtGpuBuffers {
                               * region (cbf-zero rule on eob), + three_quad_energy, scaled by the tx
                               * size (EbFullLoop.c:808-835).  Flat quantizer only.  When dist is
                               * given, qcoeff and/or dqcoeff may be NULL and are then not written. */
+    /* SURVEY 8f-4, the input of the coefficient-rate estimate (Av1TuEstimateCoeffBits,
+     * EbRateDistortionCost.c:450): */
+    uint8_t *levels;         /* optional STAGE_QUANT output: per block the padded level map exactly as
+                              * av1_txb_init_levels (EbRateDistortionCost.c:125) fills `levels_buf`:
+                              * TX_PAD_TOP = 2 zero rows, then h rows of {w levels min(|qcoeff|, 127),
+                              * TX_PAD_HOR = 4 zeros}, then TX_PAD_BOTTOM = 4 zero rows + TX_PAD_END =
+                              * 16 zeros, with w x h the coded size (64 -> 32): svtgpu_levels_size()
+                              * bytes starting at levels + levels_off[i] */
+    const uint32_t *levels_off; /* [n_blocks] byte offsets, multiples of 4 (required with levels) */
 } SvtGpuBuffers;
+/* bytes of one block's padded level map: (w + 4) * (h + 6) + 16 over the coded size */
+size_t svtgpu_levels_size(int tx_size);
 
 int svtgpu_create(SvtGpuContext **ctx, int device);
 void svtgpu_destroy(SvtGpuContext *ctx);

@@ -355,3 +355,15 @@ uint32_t ref_tx_search_mask(int tx_size, int is_inter, int reduced_tx_set_used, 
     }
     return m;
 }
+
+/* ---- av1_txb_init_levels (Codec/EbRateDistortionCost.c:125, AVX2 twin
+ * ASM_AVX2/encodetxb_avx2.c:21) on a caller buffer laid out like levels_buf ---------------------- */
+void av1_txb_init_levels_c(const tran_low_t *const coeff, const int32_t width, const int32_t height,
+    uint8_t *const levels);
+void av1_txb_init_levels_avx2(const tran_low_t *const coeff, const int32_t width, const int32_t height,
+    uint8_t *const levels);
+void ref_txb_init_levels(const int32_t *coeff, int width, int height, uint8_t *buf, int use_avx2) {
+    uint8_t *levels = buf + TX_PAD_TOP * (width + TX_PAD_HOR);   /* set_levels */
+    if (use_avx2) av1_txb_init_levels_avx2(coeff, width, height, levels);
+    else av1_txb_init_levels_c(coeff, width, height, levels);
+}

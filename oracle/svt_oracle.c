@@ -679,3 +679,22 @@ void svto_tx_search_blocks(const SvtoBlock *blk, int first, int last, const void
     fused_blocks_md(blk, first, last, src, (void *)pred, tables, qcoeff, dqcoeff, eob, energy, dist,
                     scans, clamp16, 0);
 }
+
+/* ---- av1_txb_init_levels_c (Source/Lib/Common/Codec/EbRateDistortionCost.c:125-148)
+ * on a whole levels_buf: `buf` is what the reference declares as levels_buf[TX_PAD_2D]; the
+ * reference's `levels` pointer is buf + TX_PAD_TOP * (width + TX_PAD_HOR) (set_levels, :121).
+ * Writes (width + 4) * (height + 6) + 16 bytes. */
+void svto_txb_init_levels(const int32_t *coeff, int width, int height, uint8_t *buf) {
+    const int stride = width + 4;                         /* TX_PAD_HOR */
+    uint8_t *ls = buf;
+    for (int i = 0; i < 2 * stride; ++i) *ls++ = 0;       /* TX_PAD_TOP rows */
+    for (int i = 0; i < height; ++i) {
+        for (int j = 0; j < width; ++j) {
+            int32_t a = coeff[i * width + j];
+            a = a < 0 ? -a : a;
+            *ls++ = (uint8_t)(a > 127 ? 127 : a);         /* clamp(abs, 0, INT8_MAX) */
+        }
+        for (int j = 0; j < 4; ++j) *ls++ = 0;
+    }
+    for (int i = 0; i < 4 * stride + 16; ++i) *ls++ = 0;  /* TX_PAD_BOTTOM rows + TX_PAD_END */
+}

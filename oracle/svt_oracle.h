@@ -98,6 +98,9 @@ void svto_tx_search_blocks(const SvtoBlock *blk, int first, int last, const void
                           uint64_t *energy, uint64_t *dist, const int16_t *const *scans,
                           int clamp16);
 
+/* av1_txb_init_levels_c on a whole levels_buf ((width + 4) * (height + 6) + 16 bytes) */
+void svto_txb_init_levels(const int32_t *coeff, int width, int height, uint8_t *buf);
+
 #ifdef __cplusplus
 }
 #endif

@@ -13,7 +13,8 @@ _lib = None
 
 class Buffers(ctypes.Structure):  # SvtGpuBuffers, include/svt_gpu.h
     _fields_ = [(n, ctypes.c_void_p) for n in ("residual", "pred", "recon", "coeff_in", "coeff",
-                                               "qcoeff", "dqcoeff", "eob", "energy", "src", "dist")]
+                                               "qcoeff", "dqcoeff", "eob", "energy", "src", "dist",
+                                               "levels", "levels_off")]
 
 
 def emul():
@@ -31,17 +32,21 @@ def emul():
     return _lib
 
 
-def run_emul(batch, tables, stages=7, qm=None, coeff_in=None, want_coeff=False, dist=False, coeffs=True):
+def run_emul(batch, tables, stages=7, qm=None, coeff_in=None, want_coeff=False, dist=False, coeffs=True,
+             levels_off=None):
     E = emul()
     n = batch.n_blocks
     out = dict(qcoeff=np.zeros(batch.n_coeff, np.int32) if coeffs else None,
                dqcoeff=np.zeros(batch.n_coeff, np.int32) if coeffs else None,
                eob=np.zeros(n, np.uint16), energy=np.zeros(n, np.uint64), recon=batch.pred.copy(),
                coeff=np.zeros(batch.n_coeff, np.int32) if want_coeff else None,
-               dist=np.zeros((n, 2), np.uint64) if dist else None)
+               dist=np.zeros((n, 2), np.uint64) if dist else None,
+               levels=(np.full(int(levels_off[-1]) + 2048, 0xEE, np.uint8) if levels_off is not None else None))
+    lv_off = np.ascontiguousarray(levels_off, np.uint32) if levels_off is not None else None
     b = Buffers(P(batch.residual), P(batch.pred), P(out["recon"]), P(coeff_in), P(out["coeff"]),
                 P(out["qcoeff"]), P(out["dqcoeff"]), P(out["eob"]), P(out["energy"]),
-                P(batch.src) if (stages & 16) else None, P(out["dist"]))
+                P(batch.src) if (stages & 16) else None, P(out["dist"]), P(out["levels"]),
+                P(lv_off))
     wt = iwt = off = None
     if qm is not None:
         wt, iwt, off = qm

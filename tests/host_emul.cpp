@@ -90,6 +90,7 @@ extern "C" int emul_run_batch(const SvtGpuBlock* blocks, int n, const SvtGpuBuff
     p.coeff_in = bufs->coeff_in; p.coeff_out = bufs->coeff; p.qcoeff = bufs->qcoeff;
     p.dqcoeff = bufs->dqcoeff; p.eob = bufs->eob; p.energy = bufs->energy;
     p.src = bufs->src; p.dist = reinterpret_cast<unsigned long long*>(bufs->dist);
+    p.levels = bufs->levels; p.levels_off = bufs->levels_off;
     p.qtables = qtables; p.iscan = iscan.data(); p.qm_wt = wt; p.qm_iwt = iwt;
     for (int i = 0; i < 2 * 19; ++i) (&p.qm_off[0][0])[i] = qm_off ? qm_off[i] : 0;
     for (int s = 0; s < 19; ++s)
