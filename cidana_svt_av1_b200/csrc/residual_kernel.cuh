@@ -202,9 +202,6 @@ SVT_HD constexpr int tx_id(int w, int h) {  // TxSize enum, EbDefinitions.h
 //   stage int16 [NB][H][W]     residual staged by 128-bit coalesced copies (cp.async); after the
 //                              forward column pass the same bytes hold the prediction block and
 //                              then the reconstruction (pixels), copied back out 128 bits at a time
-#ifndef SVT_R      // experiment knob: tasks per thread and phase for sizes up to 16 points
-#define SVT_R 1
-#endif
 template <int W, int H>
 struct Geo {
     static constexpr int TXS = tx_id(W, H);
@@ -217,9 +214,9 @@ struct Geo {
 #else
     static constexpr int NT = (W == H && (W == 16 || W == 32 || W == 4)) ? 256 : 128;
 #endif
-    // R: how many times a thread runs each phase (on R different blocks).  The phase loops are
-    // rolled, so the 2nd..Rth pass re-uses the instructions the first one fetched.
-    static constexpr int R = cmax(W, H) <= 16 ? SVT_R : 1;
+    // R: how many times a thread runs each phase (on R different blocks; the phase loops are
+    // rolled).  R = 2 was measured slower (fewer resident warps), see DESIGN.md section 6.
+    static constexpr int R = 1;
     static constexpr int NB = R * NT / cmin(W, H);    // blocks per CTA
     static constexpr int LD = W + 4;
     static constexpr int BLK = ((H * LD - W + 31) / 32) * 32 + W;
@@ -801,7 +798,6 @@ SVT_HD void phase_inv_col(const DevBlock& d, int c, const int* buf, void* pix) {
 }
 
 // ---- per-block staging steps shared by the kernel and the host emulation ---------------------------
-SVT_HD int px_bytes(const DevBlock& d) { return (d.meta & META_BD10) ? 2 : 1; }
 SVT_HD bool ud_flip(const DevBlock& d) { return d.meta & META_UD; }
 template <int W, int H, int NTHR, class C = CfgRuntime>
 SVT_HD void stage_residual(const KParams& p, const DevBlock& d, int16_t* sres, int tid) {

@@ -436,33 +436,5 @@ SVT_HD void identity(int (&x)[N]) {
     }
 }
 
-// ---- dispatch on the 1-D kind (0 DCT, 1 ADST, 2 identity); only kinds AV1 allows for the length
-// are instantiated (is_txfm_allowed, reference test/TxfmCommon.h:172): 64 -> DCT, 32 -> DCT/IDTX.
-template <int N, int BIT>
-SVT_HD void fwd1d(int (&x)[N], int kind) {
-    if constexpr (N == 64) {
-        fdct<N, BIT>(x);
-    } else if constexpr (N == 32) {
-        if (kind == 2) identity<N>(x); else fdct<N, BIT>(x);
-    } else {
-        if (kind == 0) fdct<N, BIT>(x);
-        else if (kind == 1) fadst<N, BIT>(x);
-        else identity<N>(x);
-    }
-}
-template <int N, class K>
-SVT_HD void inv1d(int (&x)[N], int kind, K k) {
-    constexpr int BIT = 12;  // INV_COS_BIT, EbTransforms.h:35
-    if constexpr (N == 64) {
-        idct<N, BIT>(x, k);
-    } else if constexpr (N == 32) {
-        if (kind == 2) identity<N>(x); else idct<N, BIT>(x, k);
-    } else {
-        if (kind == 0) idct<N, BIT>(x, k);
-        else if (kind == 1) iadst<N, BIT>(x, k);
-        else identity<N>(x);
-    }
-}
-
 #undef SVT_C
 }  // namespace svt
