@@ -35,6 +35,8 @@ WORKLOADS = {
     # name: (maker kwargs, description)
     "1080p8": (dict(width=1920, height=1080, n_frames=16, bd=8, seed=20240, qindex=120,
                     laplace_b=6.0), "1080p 8-bit frame batch, 16 frames, mixed TX sizes"),
+    "1080p8u": (dict(width=1920, height=1080, n_frames=16, bd=8, seed=20240, qindex=120, uniform=True),
+                "1080p 8-bit frame batch, 16 frames, residuals uniform over the full range (data independence)"),
     "4k10qm": (dict(width=3840, height=2160, n_frames=4, bd=10, seed=20241, qindex=100,
                     laplace_b=24.0, use_qm=True), "4K 10-bit frame batch with qmatrix, 4 frames"),
     "4k10": (dict(width=3840, height=2160, n_frames=4, bd=10, seed=20241, qindex=100,
