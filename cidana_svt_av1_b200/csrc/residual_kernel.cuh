@@ -202,6 +202,9 @@ SVT_HD constexpr int tx_id(int w, int h) {  // TxSize enum, EbDefinitions.h
 //   stage int16 [NB][H][W]     residual staged by 128-bit coalesced copies (cp.async); after the
 //                              forward column pass the same bytes hold the prediction block and
 //                              then the reconstruction (pixels), copied back out 128 bits at a time
+#ifndef SVT_OCC8  // experiment knob: resident 256-thread CTA equivalents for the 4- and 8-point sizes
+#define SVT_OCC8 5  // 6 (42 registers per thread) measured slower: 8x8 51.4 vs 50.5 us, 4x4 23.1 vs 21.2
+#endif
 template <int W, int H>
 struct Geo {
     static constexpr int TXS = tx_id(W, H);
@@ -235,7 +238,7 @@ struct Geo {
     // CTAs with 64 / 80 / 128 registers per thread beat more, register-starved ones (16x16: 69 vs
     // 74 us at 5 CTAs, 8x8: 58 vs 67 us at 8; 32x32: 56 us at 3 vs 60 us at 2)
     static constexpr int CTAS_PER_SM =
-        cmin((cmax(W, H) >= 64 ? 2 : (cmax(W, H) >= 32 ? 3 : (cmax(W, H) >= 16 ? 4 : 5))) * 256 / NT,
+        cmin((cmax(W, H) >= 64 ? 2 : (cmax(W, H) >= 32 ? 3 : (cmax(W, H) >= 16 ? 4 : SVT_OCC8))) * 256 / NT,
              cmax(1, (228 * 1024) / (SMEM_BYTES + 1024 + 104 * NB)));
 };
 
