@@ -214,7 +214,7 @@ int svtgpu_run_internal(SvtGpuContext* c, const SvtGpuPlan* pl, const SvtGpuBuff
     for (int s = 0; s < 19; ++s) nb += pl->count[s] > 0;
     static const int n_side = [] {  // tuning knob SVTGPU_SIDE_STREAMS (0 = every bucket on the caller's stream)
         const char* e = getenv("SVTGPU_SIDE_STREAMS");
-        const int v = e ? atoi(e) : 3;  // measured on B200 (1080p8, ms/step): 0 -> 0.352; smallest first 2 / 3 / 4 -> 0.290 / 0.287 / 0.292
+        const int v = e ? atoi(e) : 3;  // measured on B200 (1080p8, ms/step): 0 -> 0.352; smallest first 2 / 3 / 4 -> 0.290 / 0.287 / 0.292 (kernel v8); v11: 3 / 5 / 7 / 11 -> 0.248 / 0.256 / 0.279 / 0.270
         return v < 0 ? 0 : (v > SvtGpuContext::kSide ? SvtGpuContext::kSide : v);
     }();
     if (nb == 1 || n_side == 0) {
