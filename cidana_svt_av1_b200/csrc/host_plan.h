@@ -129,7 +129,7 @@ inline void build_iscan_tables(std::vector<int16_t>& all, int off[19][3]) {
 }
 
 // Validates the caller's list and buckets it by tx_size.  Inside a size bucket the caller's order is
-// kept in windows of 2^sort_window_log2() blocks, and each window is stable-sorted by tx_type: warps then
+// kept in windows of 2^sort_window_log2() blocks, and each window is stable-sorted by the 1-D kinds of the tx type: warps then
 // mostly see one type (no divergence between 1-D kinds), while blocks that are neighbours in the
 // frame -- and share 32-byte DRAM sectors of the pixel rows -- are still processed within a few
 // CTAs of each other, so the second half of a sector is an L2 hit, not another DRAM read.
@@ -161,6 +161,10 @@ inline int bucket_blocks(const SvtGpuBlock* in, int n, DevBlock* out, int first[
         valid[s] = 0;
         for (int t = 0; t < 16; ++t) valid[s] |= uint16_t(tx_pair_valid(s, t)) << t;
     }
+    // sort key of a tx type: its (column kind, row kind) pair -- the flips are data, not code, so
+    // e.g. ADST_DCT and FLIPADST_DCT run the same instructions and sort together
+    uint8_t tkey[16];
+    for (int t = 0; t < 16; ++t) tkey[t] = uint8_t(kind_of(vtx_of(t)) * 3 + kind_of(htx_of(t)));
     sc.ord.resize(size_t(n));
     uint32_t* ord = sc.ord.data();  // position of the block inside its size bucket, caller order
     int hist[19] = {};
@@ -181,7 +185,7 @@ inline int bucket_blocks(const SvtGpuBlock* in, int n, DevBlock* out, int first[
     sc.pos.assign(size_t(nkeys) + 1, 0);
     int* pos = sc.pos.data();
     for (int i = 0; i < n; ++i)
-        ++pos[key0[in[i].tx_size] + int(ord[i] >> kSortWindowLog2) * 16 + in[i].tx_type + 1];
+        ++pos[key0[in[i].tx_size] + int(ord[i] >> kSortWindowLog2) * 16 + tkey[in[i].tx_type] + 1];
     for (int k = 0; k < nkeys; ++k) pos[k + 1] += pos[k];
     for (int i = 0; i < n; ++i) {
         const SvtGpuBlock& b = in[i];
@@ -191,7 +195,7 @@ inline int bucket_blocks(const SvtGpuBlock* in, int n, DevBlock* out, int first[
         d.coeff_off = b.coeff_off; d.qrow = b.qrow; d.id = uint32_t(i);
         d.meta = make_meta(b.tx_type, b.bit_depth, b.plane, b.flags & SVTGPU_BLK_CLAMP16,
                            b.flags & SVTGPU_BLK_USE_QM);
-        out[pos[key0[b.tx_size] + int(ord[i] >> kSortWindowLog2) * 16 + b.tx_type]++] = d;
+        out[pos[key0[b.tx_size] + int(ord[i] >> kSortWindowLog2) * 16 + tkey[b.tx_type]]++] = d;
     }
     return 0;
 }
