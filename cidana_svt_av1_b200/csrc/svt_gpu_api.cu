@@ -238,14 +238,18 @@ int svtgpu_run_internal(SvtGpuContext* c, const SvtGpuPlan* pl, const SvtGpuBuff
     // ms/step for largest first on three streams); 0 = largest first; 2 = the four largest round
     // robin over the first n_side - 1 streams, everything else on the last stream (0.318)
     static const int order_mode = [] { const char* e = getenv("SVTGPU_ORDER"); return e ? atoi(e) : 1; }();
+    // 3 = smallest first; the four largest queue behind each other on stream 0 (two big grids never
+    // share the SMs), the rest round robin over the other streams
     bool used[SvtGpuContext::kSide] = {};
-    int rank_of = 0;
+    int rank_of = 0, n_present = 0;
+    for (int s = 0; s < 19; ++s) n_present += pl->count[s] > 0;
     for (int ii = 0; ii < 19; ++ii) {
-        const int i = order_mode == 1 ? 18 - ii : ii;
+        const int i = (order_mode == 1 || order_mode == 3) ? 18 - ii : ii;
         const int s = order[i];
         if (!pl->count[s]) continue;
         int si = k++ % n_side;
         if (order_mode == 2 && n_side >= 2) si = rank_of < 4 ? rank_of % (n_side - 1) : n_side - 1;
+        if (order_mode == 3 && n_side >= 2) si = rank_of >= n_present - 4 ? 0 : 1 + rank_of % (n_side - 1);
         ++rank_of;
         if (!used[si]) { CK(cudaStreamWaitEvent(c->side[si], c->fork, 0)); used[si] = true; }
         CK(launch_bucket(s, p, pl->first[s], pl->count[s], c->side[si]));
