@@ -182,6 +182,29 @@ int svtgpu_submit_host(SvtGpuContext *ctx, const SvtGpuHostFrame *frame, int sta
 /* blocks until submission `ticket` (or all of them when ticket < 0) has fully landed in host memory */
 int svtgpu_wait_host(SvtGpuContext *ctx, int ticket);
 
+/* ---- allocation-free quantizer ---------------------------------------------------------------
+ * No counterpart in the reference: this entry point was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same arithmetic and results as the level-A slots
+ * svtgpu_aom_highbd_quantize_b / _32x32 / _64x64 (log_scale 0 / 1 / 2), but:
+ *   - d_coeff, d_qcoeff, d_dqcoeff, d_eob (one uint16) and d_iscan are DEVICE pointers of the
+ *     current device; the five table rows are host pointers ([0] DC, [1] AC are read, by value);
+ *   - asynchronous on `cuda_stream` (a cudaStream_t; NULL = the default stream);
+ *   - it calls no cudaMalloc / cudaFree / allocating routine: its only working memory is a 256-byte
+ *     file-scope __device__ array (csrc/svt_gpu_noalloc.cu) that every GPU loading the library
+ *     holds until exit, whose address is resolved once per device on the first call there (make
+ *     that first call outside graph capture);
+ *   - n_coeffs above SVTGPU_NOALLOC_MAX_COEFFS is rejected with SVTGPU_ERR_ARG and a message in
+ *     svtgpu_last_error();
+ *   - every call on a GPU shares that array: calls that overlap on one GPU (different streams or
+ *     threads) race on it and must be serialised by the caller. */
+#define SVTGPU_NOALLOC_MAX_COEFFS 32768
+int svtgpu_quantize_b_noalloc(const int32_t *d_coeff, intptr_t n_coeffs, int log_scale,
+                              const int16_t *zbin, const int16_t *round, const int16_t *quant,
+                              const int16_t *quant_shift, const int16_t *dequant,
+                              int32_t *d_qcoeff, int32_t *d_dqcoeff, uint16_t *d_eob,
+                              const int16_t *d_iscan, void *cuda_stream);
+
 /* scan tables the library generates (av1_scan_orders, EbTransforms.h:3349): for tests */
 int svtgpu_get_iscan(int tx_size, int scan_class, int16_t *iscan_out /* max_eob entries */);
 
