@@ -110,19 +110,42 @@ def make_cpu_runner(batch, tables, qm):
     return CpuRunner(batch, tables, scans=load_scans(), qm=qm)
 
 
-def cpu_baseline(batch, tables, qm, budget_s=12.0):
-    """The reference compiled from source (oracle/_ref, kind 'reference') when present and
-    applicable, else the oracle port, on all host cores; best pass within a bounded time."""
+def config_for(workload, batch, world):
+    """The `config` object of a JSON line: one function for both arms, so that the driver sees the
+    same workload under the same keys."""
+    return {"workload": WORKLOADS[workload][1], "name": batch.name,
+            "samples_per_step_per_gpu": batch.n_samples, "blocks_per_gpu": batch.n_blocks,
+            "bytes_per_step_per_gpu": batch.algorithmic_bytes(),
+            "l2": "inputs+outputs per step (>= 550 MB) exceed the 126 MB L2; no flush needed",
+            "parallelism": f"frames sharded over {world} GPU(s), no collective"}
+
+
+def cpu_measure(runner, cores, budget_s, min_passes=3, max_passes=200):
+    """Passes of the persistent-pool reference over the whole batch within a time budget:
+    (mean seconds, best seconds, passes).  One untimed pass first (page faults, pool start)."""
+    runner.run(cores)
+    times, t_start = [], time.perf_counter()
+    while len(times) < min_passes or (time.perf_counter() - t_start < budget_s and len(times) < max_passes):
+        times.append(runner.run(cores))
+    return float(np.mean(times)), float(np.min(times)), len(times)
+
+
+def cpu_baseline(batch, tables, qm, budget_s=8.0, runner=None):
+    """The reference compiled from source (oracle/_ref, kind 'reference': its AVX2 RTCD path, and
+    highbd_quantize_b_helper_c where a qmatrix applies) on a persistent pthread pool over all host
+    cores; `value` is the MEAN pass (what --impl reference reports), `best` the best pass, and
+    `one_thread` the same code on one core over the first sixteenth of the block list."""
     cores = os.cpu_count() or 1
-    runner = make_cpu_runner(batch, tables, qm)
-    best, passes, t_start = None, 0, time.perf_counter()
-    while passes < 2 or (time.perf_counter() - t_start < budget_s and passes < 200):
-        dt = runner.run(cores)
-        best = dt if best is None else min(best, dt)
-        passes += 1
-    return {"value": batch.n_samples / best / 1e6, "unit": UNIT, "cores": cores, "kind": runner.kind,
-            "sample": f"{passes} passes over the full {batch.name} batch ({batch.n_samples} samples), "
-                      f"best pass, {cores} threads"}
+    runner = runner or make_cpu_runner(batch, tables, qm)
+    mean, best, passes = cpu_measure(runner, cores, budget_s)
+    n1 = max(1, batch.n_blocks // 16)
+    s1 = int(wl.AREA[batch.blocks["tx_size"][:n1]].sum())
+    t1 = min(runner.run(1, n1) for _ in range(3))
+    return {"value": batch.n_samples / mean / 1e6, "best": batch.n_samples / best / 1e6,
+            "one_thread": s1 / t1 / 1e6, "unit": UNIT, "cores": cores, "kind": runner.kind,
+            "sample": f"{passes} passes over the full {batch.name} batch ({batch.n_samples} samples) on a "
+                      f"persistent {cores}-thread pool: mean (value) and best pass; one_thread = the first "
+                      f"{n1} blocks ({s1} samples) on one core, best of 3"}
 
 
 def reference_arm(args, rank, world):
@@ -130,22 +153,23 @@ def reference_arm(args, rank, world):
     compiled, else the oracle port) on all host threads; each step = one pass over the workload."""
     if rank != 0:
         return 0
-    batch = make_batch(args.workload, 0)
+    batch = make_batch(args.workload, 0, args.gpus)
     tables = load_tables(batch.bd)
     qm = load_qm() if "qm" in args.workload else None
     cores = os.cpu_count() or 1
     runner = make_cpu_runner(batch, tables, qm)
-    for _ in range(args.warmup):
+    for _ in range(max(args.warmup, 1)):
         runner.run(cores)
-    t = sum(runner.run(cores) for _ in range(args.steps))
+    each = [runner.run(cores) for _ in range(args.steps)]
+    t = sum(each)
     val = batch.n_samples * args.steps / t / 1e6
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32",
-            "data": "synthetic", "config": {"workload": WORKLOADS[args.workload][1], "name": batch.name,
-                                            "samples_per_step": batch.n_samples, "blocks": batch.n_blocks},
-            "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": runner.kind,
-                             "sample": f"each step = one pass over the full batch, {cores} threads"},
+            "data": "synthetic", "config": config_for(args.workload, batch, args.gpus),
+            "cpu_baseline": {"value": val, "best": batch.n_samples / min(each) / 1e6, "unit": UNIT, "cores": cores,
+                             "kind": runner.kind,
+                             "sample": f"each step = one pass over the full batch on a persistent {cores}-thread pool"},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     emit(line)
     return 0
@@ -210,6 +234,186 @@ def mode_arm(args, local_rank):
     return 0
 
 
+PARITY_KEYS = ("qcoeff", "dqcoeff", "eob", "energy", "recon")
+
+
+class DeviceJob:
+    """One workload resident on this rank's GPU: plan, device buffers, the step, and the checks."""
+
+    def __init__(self, pkg, g, batch, tables, qm, dev, st):
+        import torch
+        self.torch, self.pkg, self.g, self.batch, self.tables, self.qm, self.dev, self.st = \
+            torch, pkg, g, batch, tables, qm, dev, st
+        self.plan = g.plan(batch.blocks)
+        pdt = np.uint8 if batch.bd == 8 else np.int16
+        with torch.cuda.stream(st):
+            d = dict(residual=torch.from_numpy(batch.residual).to(dev),
+                     pred=torch.from_numpy(batch.pred.view(pdt)).to(dev))
+            d["recon"] = torch.empty_like(d["pred"])
+            d["qcoeff"] = torch.empty(batch.n_coeff, dtype=torch.int32, device=dev)
+            d["dqcoeff"] = torch.empty(batch.n_coeff, dtype=torch.int32, device=dev)
+            d["eob"] = torch.empty(batch.n_blocks, dtype=torch.int16, device=dev)
+            d["energy"] = torch.empty(batch.n_blocks, dtype=torch.int64, device=dev)
+        st.synchronize()
+        self.d = d
+        self._runner = None
+
+    def step(self, plan=None):
+        self.g.run(plan or self.plan, self.pkg.api.STAGE_ALL, self.st.cuda_stream, **self.d)
+
+    def timed(self, steps, barrier):
+        """`steps` steps between two CUDA events on the launching stream -> (ms, launches)."""
+        torch = self.torch
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = self.g.launches
+        barrier()
+        e0.record(self.st)
+        for _ in range(steps):
+            self.step()
+        e1.record(self.st)
+        barrier()
+        return e0.elapsed_time(e1), self.g.launches - l0
+
+    def outputs(self):
+        d, b = self.d, self.batch
+        self.st.synchronize()
+        return dict(qcoeff=d["qcoeff"].cpu().numpy(), dqcoeff=d["dqcoeff"].cpu().numpy(),
+                    eob=d["eob"].cpu().numpy().view(np.uint16), energy=d["energy"].cpu().numpy().view(np.uint64),
+                    recon=d["recon"].cpu().numpy().view(b.pred.dtype))
+
+    def runner(self):
+        if self._runner is None:
+            self._runner = make_cpu_runner(self.batch, self.tables, self.qm)
+        return self._runner
+
+    def parity(self, got=None):
+        """what was timed must be byte-identical to the CPU run.  The outputs
+        the timed steps left on the device (or `got`, host arrays of the e2e call) against ONE fresh
+        pass of the compiled reference over the same batch, every block, every output."""
+        r = self.runner()
+        r.reset()
+        r.run(os.cpu_count() or 1)
+        want, got = r.outputs(), got or self.outputs()
+        bad = [k for k in PARITY_KEYS if not np.array_equal(got[k], want[k])]
+        return {"checked_blocks": self.batch.n_blocks, "vs": r.kind, "ok": not bad, "mismatch": bad}
+
+    def time_bucket(self, tx_size, reps=20):
+        """One size bucket alone on the launching stream: (ms per launch, algorithmic bytes)."""
+        torch, batch = self.torch, self.batch
+        sizes = batch.blocks["tx_size"]
+        sub_blocks = batch.blocks[sizes == tx_size]
+        sub = wl.Batch(sub_blocks, batch.residual, batch.pred, batch.n_coeff, batch.bd, "bucket")
+        pl = self.g.plan(sub_blocks)
+        for _ in range(3):
+            self.step(pl)
+        k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        self.st.synchronize()
+        k0.record(self.st)
+        for _ in range(reps):
+            self.step(pl)
+        k1.record(self.st)
+        self.st.synchronize()
+        pl.close()
+        return k0.elapsed_time(k1) / reps, sub.algorithmic_bytes()
+
+    def close(self):
+        self.plan.close()
+        self.d = None
+
+
+def all_ok(flag, world, dev):
+    """True only if every rank's flag is true."""
+    import torch
+    import torch.distributed as dist
+    t = torch.tensor([1.0 if flag else 0.0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    return bool(t.item() > 0.5)
+
+
+def int32_record(workload, kernel):
+    """The secondary (integer-pipe) roofline from the kept ncu capture of this kernel version
+    (profiles/int32.json: ALU / FMA pipe and issue-slot utilisation, thread instructions per
+    sample); static, labelled with the capture it came from."""
+    f = os.path.join(ROOT, "profiles", "int32.json")
+    try:
+        return json.load(open(f)).get(f"{workload}:{kernel}")
+    except Exception:
+        return None
+
+
+def extra_workload(pkg, local_rank, rank, world, dev, st, name, steps, barrier):
+    """A secondary workload (BASELINE configs 4 / 4'): device-resident steps, whole-step roofline,
+    parity gate.  Own context: its tables and qmatrix differ from the headline's."""
+    batch = make_batch(name, rank, world)
+    tables = load_tables(batch.bd)
+    qm = load_qm() if "qm" in name else None
+    g = pkg.SvtGpu(local_rank)
+    g.upload_quant_tables(tables)
+    if qm is not None:
+        g.upload_qmatrix(*qm)
+    job = DeviceJob(pkg, g, batch, tables, qm, dev, st)
+    for _ in range(3):
+        job.step()
+    ms, launches = job.timed(steps, barrier)
+    par = job.parity()
+    ok = all_ok(par["ok"], world, dev)
+    ms, total = sharding.reduce_step(ms, batch.n_samples, world, dev)
+    hbm, _ = peaks()
+    gbs = batch.algorithmic_bytes() / (ms / steps * 1e-3) / 1e9
+    rec = {"workload": WORKLOADS[name][1], "name": batch.name,
+           "value": sharding.throughput_mcoeff(total, steps, ms) if ok else None, "unit": UNIT,
+           "ms_per_step": ms / steps, "steps": steps, "samples_per_step_per_gpu": batch.n_samples,
+           "roofline": {"bound": "hbm", "scope": "whole step", "achieved": gbs, "peak": hbm, "unit": "GB/s",
+                        "frac": gbs / hbm, "algorithmic_bytes_per_step": batch.algorithmic_bytes()},
+           "parity": dict(par, ok=ok, ranks=world), "gpu_launches": launches}
+    if rank == 0 and world == 1:
+        c = cpu_baseline(batch, tables, qm, budget_s=3.0, runner=job.runner())
+        rec["cpu_baseline"] = c
+    job.close()
+    g.close()
+    return rec
+
+
+def sweep(pkg, g8, local_rank, dev, st):
+    """BASELINE config 2 on one GPU: for every TX size and bit depth, all its legal tx types x 4096
+    blocks (1024 for the 32- and 64-point sizes), uniform full-range residuals, one
+    launch: throughput, HBM fraction and parity against the compiled reference per (size, bd)."""
+    torch = __import__("torch")
+    out = {}
+    hbm, _ = peaks()
+    for bd in (8, 10):
+        tables = load_tables(bd)
+        g = g8 if bd == 8 else pkg.SvtGpu(local_rank)
+        if bd != 8:
+            g.upload_quant_tables(tables)
+        for s_ in range(19):
+            pairs = [(s_, t) for t in range(16) if wl.is_valid(s_, t)]
+            n_per = 1024 if max(wl.TX_W[s_], wl.TX_H[s_]) >= 32 else 4096
+            batch = wl.make_packed_batch(pairs, bd, n_per, seed=13596 + 19 * bd + s_)
+            job = DeviceJob(pkg, g, batch, tables, None, dev, st)
+            for _ in range(3):
+                job.step()
+            reps = 10
+            k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            st.synchronize()
+            k0.record(st)
+            for _ in range(reps):
+                job.step()
+            k1.record(st)
+            st.synchronize()
+            ms = k0.elapsed_time(k1) / reps
+            par = job.parity()
+            gbs = batch.algorithmic_bytes() / ms / 1e6
+            out[f"{wl.TX_W[s_]}x{wl.TX_H[s_]}_bd{bd}"] = {
+                "Mcoeff/s": round(batch.n_samples / ms / 1e3, 1) if par["ok"] else None, "us": round(ms * 1e3, 2),
+                "frac": round(gbs / hbm, 3), "blocks": batch.n_blocks, "tx_types": len(pairs), "parity_ok": par["ok"]}
+            job.close()
+        if bd != 8:
+            g.close()
+    return out
+
+
 def gpu_arm(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
@@ -226,22 +430,8 @@ def gpu_arm(args, rank, world, local_rank):
     g.upload_quant_tables(tables)
     if qm is not None:
         g.upload_qmatrix(*qm)
-    plan = g.plan(batch.blocks)
     st = torch.cuda.Stream(dev)
-    pdt = np.uint8 if batch.bd == 8 else np.int16
-    with torch.cuda.stream(st):
-        h_res = torch.from_numpy(batch.residual).pin_memory()
-        h_pred = torch.from_numpy(batch.pred.view(pdt)).pin_memory()
-        d = dict(residual=h_res.to(dev), pred=h_pred.to(dev))
-        d["recon"] = torch.empty_like(d["pred"])
-        d["qcoeff"] = torch.empty(batch.n_coeff, dtype=torch.int32, device=dev)
-        d["dqcoeff"] = torch.empty(batch.n_coeff, dtype=torch.int32, device=dev)
-        d["eob"] = torch.empty(batch.n_blocks, dtype=torch.int16, device=dev)
-        d["energy"] = torch.empty(batch.n_blocks, dtype=torch.int64, device=dev)
-    st.synchronize()
-
-    def step():
-        g.run(plan, pkg.api.STAGE_ALL, st.cuda_stream, **d)
+    job = DeviceJob(pkg, g, batch, tables, qm, dev, st)
 
     def barrier():
         st.synchronize()
@@ -250,36 +440,42 @@ def gpu_arm(args, rank, world, local_rank):
         torch.cuda.synchronize()
 
     for _ in range(max(args.warmup, 3)):
-        step()
+        job.step()
     barrier()
     sampler = ClockSampler(local_rank) if rank == 0 else None
     if sampler:
         sampler.start()
         time.sleep(0.3)
-    l0 = g.launches
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    e0.record(st)
-    for _ in range(args.steps):
-        step()
-    e1.record(st)
-    barrier()
-    ms = e0.elapsed_time(e1)
-    launches = g.launches - l0
+    ms, launches = job.timed(args.steps, barrier)
+    sustained = None
     if sampler:
-        # keep the GPU busy a little longer so the 100 ms sampler sees clocks under load
-        t_end = time.time() + 1.0
-        while time.time() < t_end:
-            step()
-        st.synchronize()
+        # a seconds-long run of the same step: the clock sampler (100 ms period) sees the GPU under
+        # load, and the figure shows whether the short timed region above flatters the kernel
+        n_sus = max(args.steps, int(1.5 / max(ms / args.steps * 1e-3, 1e-6)))
+        ms_sus, _ = job.timed(n_sus, lambda: st.synchronize())
+        sustained = {"steps": n_sus, "ms_per_step": ms_sus / n_sus,
+                     "value": batch.n_samples * n_sus / (ms_sus * 1e-3) / 1e6}
     clocks = sampler.finish() if sampler else None
+    # parity gate: the outputs the timed steps left on the device, every block, every rank
+    par = job.parity()
+    parity_ok = all_ok(par["ok"], world, dev)
+    if not par["ok"]:
+        print(f"rank {rank}: PARITY MISMATCH vs {par['vs']} in {par['mismatch']}", file=sys.stderr, flush=True)
     ms, total_samples = sharding.reduce_step(ms, batch.n_samples, world, dev)
     value = sharding.throughput_mcoeff(total_samples, args.steps, ms)
+    if not parity_ok:
+        if rank == 0:
+            emit({"metric": METRIC, "value": None, "unit": UNIT, "n_gpus": world,
+                  "parity": dict(par, ok=False, ranks=world),
+                  "error": "GPU outputs differ from the reference: no throughput is reported (BASELINE.md section 3)"})
+        if world > 1:
+            dist.destroy_process_group()
+        return 3
 
     if args.kernel_only:
         if rank == 0:
             emit({"metric": METRIC, "value": value, "unit": UNIT, "ms_per_step": ms / args.steps,
-                  "gpu_launches": launches, "kernel_only": True})
+                  "gpu_launches": launches, "kernel_only": True, "parity": dict(par, ranks=world)})
         return 0
 
     # ---- roofline of the dominant kernel, timed alone on the launching stream --------------------
@@ -287,43 +483,29 @@ def gpu_arm(args, rank, world, local_rank):
     sizes = batch.blocks["tx_size"]
     by_size = {int(s): int((wl.AREA[sizes[sizes == s]]).sum()) for s in np.unique(sizes)}
     dom = max(by_size, key=by_size.get)
-
-    def time_bucket(tx_size, reps=20):
-        """One size bucket alone on the launching stream: (ms per launch, algorithmic bytes)."""
-        sub_blocks = batch.blocks[sizes == tx_size]
-        sub = wl.Batch(sub_blocks, batch.residual, batch.pred, batch.n_coeff, batch.bd, "bucket")
-        pl = g.plan(sub_blocks)
-        for _ in range(3):
-            g.run(pl, pkg.api.STAGE_ALL, st.cuda_stream, **d)
-        k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        st.synchronize()
-        k0.record(st)
-        for _ in range(reps):
-            g.run(pl, pkg.api.STAGE_ALL, st.cuda_stream, **d)
-        k1.record(st)
-        st.synchronize()
-        pl.close()
-        return k0.elapsed_time(k1) / reps, sub.algorithmic_bytes()
-
-    k_ms, k_bytes = time_bucket(dom)
+    k_ms, k_bytes = job.time_bucket(dom)
     achieved = k_bytes / (k_ms * 1e-3) / 1e9
     per_kernel = None
     if args.per_kernel and rank == 0:
         per_kernel = {}
         for s_ in sorted(by_size, key=by_size.get, reverse=True):
-            t_, b_ = time_bucket(s_)
+            t_, b_ = job.time_bucket(s_)
             per_kernel[f"{wl.TX_W[s_]}x{wl.TX_H[s_]}"] = {"us": round(t_ * 1e3, 2), "GB/s": round(b_ / t_ / 1e6, 1),
                                                         "frac": round(b_ / t_ / 1e6 / hbm, 3)}
         print("per-kernel (each bucket alone):", json.dumps(per_kernel), file=sys.stderr, flush=True)
-    roof = {"bound": "hbm", "kernel": f"residual_kernel<{wl.TX_W[dom]},{wl.TX_H[dom]}>",
+    kname = f"residual_kernel<{wl.TX_W[dom]},{wl.TX_H[dom]}>"
+    roof = {"bound": "hbm", "kernel": kname,
             "achieved": achieved, "peak": hbm, "peak_source": which, "unit": "GB/s", "frac": achieved / hbm,
-            "traffic": None, "launch_ms": k_ms, "algorithmic_bytes_per_launch": k_bytes,
+            "traffic": None, "traffic_source": None, "launch_ms": k_ms, "algorithmic_bytes_per_launch": k_bytes,
             "step_achieved": batch.algorithmic_bytes() / (ms / args.steps * 1e-3) / 1e9,
-            "step_frac": batch.algorithmic_bytes() / (ms / args.steps * 1e-3) / 1e9 / hbm}
+            "step_frac": batch.algorithmic_bytes() / (ms / args.steps * 1e-3) / 1e9 / hbm,
+            "int32": int32_record(args.workload, kname)}
     tf = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tf):
         try:
-            roof["traffic"] = json.load(open(tf)).get(f"{args.workload}:{roof['kernel']}")
+            tj = json.load(open(tf))
+            roof["traffic"] = tj.get(f"{args.workload}:{kname}")
+            roof["traffic_source"] = tj.get("_source")
         except Exception:
             pass
 
@@ -351,32 +533,45 @@ def gpu_arm(args, rank, world, local_rank):
         e2e_step()
         e2e_each.append((round((time.perf_counter() - t1) * 1e3, 2), int(L.svtgpu_debug_host_allocs())))
     barrier()
+    e2e_wall = time.perf_counter() - t0
     if rank == 0:
         print("e2e ms per step:", e2e_each, file=sys.stderr, flush=True)
-    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    e2e_s = torch.tensor([e2e_wall], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     e2e_val = total_samples * e2e_steps / float(e2e_s.item()) / 1e6
+    # the host arrays the e2e call filled go through the same gate
+    e2e_par = job.parity({k: hb.out[k] for k in PARITY_KEYS})
+    e2e_ok = all_ok(e2e_par["ok"], world, dev)
+
+    extra = {}
+    if not args.no_extra:
+        x_steps = max(3, min(args.steps, 10))
+        for name in ("4k10qm", "4k10"):
+            if name != args.workload:
+                extra[name] = extra_workload(pkg, local_rank, rank, world, dev, st, name, x_steps, barrier)
+        if world == 1 and batch.bd == 8 and qm is None:
+            extra["sweep"] = sweep(pkg, g, local_rank, dev, st)
 
     if rank == 0:
         cpu = None
         if world == 1 and not args.no_cpu:
-            cpu = cpu_baseline(batch, tables, qm)
+            cpu = cpu_baseline(batch, tables, qm, runner=job.runner())
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
-                "config": {"workload": WORKLOADS[args.workload][1], "name": batch.name,
-                           "samples_per_step_per_gpu": batch.n_samples, "blocks_per_gpu": batch.n_blocks,
-                           "bytes_per_step_per_gpu": batch.algorithmic_bytes(),
-                           "l2": "inputs+outputs per step (>= 550 MB) exceed the 126 MB L2; no flush needed",
-                           "parallelism": f"frames sharded over {world} GPU(s), no collective"},
-                "roofline": roof, "cpu_baseline": cpu, "clocks": clocks, "gpu_launches": launches,
-                "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
-                        "d2h_bytes_per_step": int(d2h), "steps": e2e_steps}}
+                "config": config_for(args.workload, batch, world),
+                "parity": dict(par, ok=True, ranks=world),
+                "roofline": roof, "cpu_baseline": cpu, "clocks": clocks, "sustained": sustained,
+                "gpu_launches": launches,
+                "e2e": {"value": e2e_val if e2e_ok else None, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+                        "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
+                        "parity": dict(e2e_par, ok=e2e_ok, ranks=world)},
+                "extra": extra}
         emit(line)
     if world > 1:
         dist.destroy_process_group()
-    return 0
+    return 0 if e2e_ok else 3
 
 
 _REAL_STDOUT = None
@@ -409,6 +604,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="1080p8", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-extra", action="store_true", help="skip the secondary workloads (4k10qm, 4k10, sweep)")
     ap.add_argument("--per-kernel", action="store_true", help="time every size bucket alone (stderr)")
     ap.add_argument("--mode", default="fused", choices=["fused", "md", "txsearch"],
                     help="fused = the headline path; md / txsearch = the SURVEY 8f rows (N = 1, extra lines)")

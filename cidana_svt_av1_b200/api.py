@@ -37,7 +37,7 @@ class _HostFrame(ctypes.Structure):  # SvtGpuHostFrame
                 ("pred", ctypes.c_void_p), ("recon", ctypes.c_void_p), ("pixel_elems", ctypes.c_size_t),
                 ("qcoeff", ctypes.c_void_p), ("dqcoeff", ctypes.c_void_p), ("coeff_elems", ctypes.c_size_t),
                 ("eob", ctypes.c_void_p), ("energy", ctypes.c_void_p), ("src", ctypes.c_void_p),
-                ("dist", ctypes.c_void_p)]
+                ("dist", ctypes.c_void_p), ("plan", ctypes.c_void_p)]
 
 
 _lib = None
@@ -160,7 +160,7 @@ class SvtGpu:
         once, reuse for every run over batches of this geometry."""
         return HostBuffers(batch, pinned, dist, coeffs)
 
-    def submit_host(self, frame, out, stages=STAGE_ALL, residual=None, pred=None, src=None):
+    def submit_host(self, frame, out, stages=STAGE_ALL, residual=None, pred=None, src=None, plan=None):
         """Queue one picture (a Batch whose offsets are relative to its own arrays) on the
         pipeline; `out` is a dict of host arrays (qcoeff, dqcoeff, eob, energy, recon and
         optionally dist) sized for this picture; qcoeff / dqcoeff may be None next to dist.
@@ -179,7 +179,7 @@ class SvtGpu:
                         residual.size if residual is not None else 0, _P(pred).value,
                         _P(out["recon"]).value, pred.size, opt("qcoeff"), opt("dqcoeff"), frame.n_coeff,
                         _P(out["eob"]).value, opt("energy"), _P(src).value if src is not None else None,
-                        opt("dist"))
+                        opt("dist"), plan.handle if plan is not None else None)
         t = ctypes.c_int(-1)
         _check(lib().svtgpu_submit_host(self.handle, ctypes.byref(hf), int(stages), ctypes.byref(t)),
                "svtgpu_submit_host")
@@ -188,16 +188,21 @@ class SvtGpu:
     def wait_host(self, ticket=-1):
         _check(lib().svtgpu_wait_host(self.handle, int(ticket)), "svtgpu_wait_host")
 
-    def run_host(self, batch, stages=STAGE_ALL, bufs=None):
+    def run_host(self, batch, stages=STAGE_ALL, bufs=None, plans=None):
         """Host arrays in, host arrays out, every copy included: each picture of the batch goes
         through svtgpu_submit_host (upload, kernels and download of consecutive pictures overlap),
-        then one wait.  Returns a dict of numpy arrays like the oracle runners do."""
+        then one wait.  Returns a dict of numpy arrays like the oracle runners do.
+        plans: one Plan per picture (frame_plans), for callers whose geometry repeats."""
         bufs = bufs or HostBuffers(batch, pinned=False)
         for k, fr in enumerate(batch.frames()):
             res, pred, src = bufs.frame_in(k)
-            self.submit_host(fr, bufs.frame_out(k), stages, res, pred, src)
+            self.submit_host(fr, bufs.frame_out(k), stages, res, pred, src, plans[k] if plans else None)
         self.wait_host()
         return bufs.out
+
+    def frame_plans(self, batch):
+        """One reusable plan per picture of the batch (offsets relative to the picture)."""
+        return [self.plan(fr.blocks) for fr in batch.frames()]
 
     def tx_search(self, batch, is_inter=0, reduced_tx_set_used=0, tx_search_reduced_set=0,
                   want_coeff=False):

@@ -58,16 +58,42 @@ int slot_wait(HostSlot& s) {
         if (rc_ != SVTGPU_OK) return rc_; \
     } while (0)
 
+// fault injection for the tests: the k-th grow() from now on fails as if the device were out of
+// memory (0 = off).  Not declared in the public header.
+static int g_fail_grow_in = 0;
+extern "C" void svtgpu_debug_fail_host_alloc(int kth) { g_fail_grow_in = kth; }
+
+namespace {
+template <class T>
+int grow_checked(T*& p, size_t& cap, size_t need, cudaStream_t st, size_t headroom_div = 4) {
+    if (need > cap && g_fail_grow_in > 0 && --g_fail_grow_in == 0) {
+        // behave exactly like a failed cudaMalloc inside grow(): old buffer gone, capacity 0
+        CK(cudaStreamSynchronize(st));
+        if (p) CK(cudaFree(p));
+        p = nullptr;
+        cap = 0;
+        svtgpu_set_error("%s%s (line %d)", "out of device memory in the host pipeline", " (injected)", __LINE__);
+        return SVTGPU_ERR_NOMEM;
+    }
+    return grow(p, cap, need, st, headroom_div);
+}
+}  // namespace
+
 extern "C" int svtgpu_submit_host(SvtGpuContext* c, const SvtGpuHostFrame* f, int stages, int* ticket) {
-    if (!c || !f || f->n_blocks < 0 || (f->n_blocks && !f->blocks)) return SVTGPU_ERR_ARG;
+    if (!c || !f || f->n_blocks < 0 || (f->n_blocks && !f->blocks && !f->plan)) return SVTGPU_ERR_ARG;
     if (!(stages & SVTGPU_STAGE_ALL) || (stages & ~(SVTGPU_STAGE_ALL | SVTGPU_STAGE_RESIDUAL))) return SVTGPU_ERR_ARG;
     if (f->bit_depth != 8 && f->bit_depth != 10) return SVTGPU_ERR_ARG;
     const bool fwd = stages & STAGE_FWD, qnt = stages & STAGE_QUANT, inv = stages & STAGE_INV;
     if (!fwd || !qnt) return SVTGPU_ERR_ARG;  // the pipeline carries the fused path (optionally without INV)
     const bool diff = stages & SVTGPU_STAGE_RESIDUAL;
     if (!f->eob || (diff ? (!f->src || !f->pred) : !f->residual)) return SVTGPU_ERR_ARG;
-    if (!f->dist && (!f->qcoeff || !f->dqcoeff)) return SVTGPU_ERR_ARG;
+    if (!f->dist && !f->qcoeff) return SVTGPU_ERR_ARG;  // dqcoeff alone is never useful; either may be absent next to dist
+    if (f->dqcoeff && !f->qcoeff) return SVTGPU_ERR_ARG;
     if (inv && (!f->pred || !f->recon)) return SVTGPU_ERR_ARG;
+    if (f->plan && (f->plan->ctx != c || f->plan->n != f->n_blocks)) {
+        svtgpu_set_error("%s%s (line %d)", "SvtGpuHostFrame.plan belongs to another context or block count", "", __LINE__);
+        return SVTGPU_ERR_ARG;
+    }
     CK(cudaSetDevice(c->device));
     HostSlot& s = c->host[c->host_next];
     c->host_next = (c->host_next + 1) % SvtGpuContext::kHostSlots;
@@ -79,62 +105,89 @@ extern "C" int svtgpu_submit_host(SvtGpuContext* c, const SvtGpuHostFrame* f, in
     if (ticket) *ticket = my_ticket;
     if (n == 0) return SVTGPU_OK;
 
-    // descriptors: validate + bucket on the host, straight into page-locked staging
-    SvtGpuPlan plan;
-    plan.ctx = c;
-    plan.n = n;
-    if (size_t(n) > s.cap_blocks) {
-        CK(cudaStreamSynchronize(s.st));
-        ++g_host_allocs;
-        if (s.h_blocks) CK(cudaFreeHost(s.h_blocks));
-        s.h_blocks = nullptr;
-        CK(cudaMallocHost(reinterpret_cast<void**>(&s.h_blocks), size_t(n) * 2 * sizeof(DevBlock)));
+    SvtGpuPlan local;
+    const SvtGpuPlan* plan = f->plan;
+    if (plan) {
+        // a plan made once for this picture geometry (svtgpu_plan_create): descriptors are already
+        // validated, sorted and resident; nothing is re-bucketed or uploaded per submission
+        if (plan->bd_uniform != f->bit_depth) return SVTGPU_ERR_ARG;
+        if ((!diff && plan->need_res > f->residual_elems) || plan->need_pix > f->pixel_elems ||
+            plan->need_coeff > f->coeff_elems) {
+            svtgpu_set_error("%s%s (line %d)", "a block of the plan reaches beyond residual_elems / pixel_elems / coeff_elems", "", __LINE__);
+            return SVTGPU_ERR_ARG;
+        }
+    } else {
+        // descriptors: validate + bucket on the host, straight into page-locked staging
+        local.ctx = c;
+        local.n = n;
+        if (size_t(n) > s.cap_hblocks) {
+            CK(cudaStreamSynchronize(s.st));
+            ++g_host_allocs;
+            if (s.h_blocks) CK(cudaFreeHost(s.h_blocks));
+            s.h_blocks = nullptr;
+            s.cap_hblocks = 0;
+            CK(cudaMallocHost(reinterpret_cast<void**>(&s.h_blocks), size_t(n) * 2 * sizeof(DevBlock)));
+            s.cap_hblocks = size_t(n) * 2;
+        }
+        // per-block buffers are small (32 + 26 bytes per block) and the block count of a picture moves
+        // with its partitioning: 2x headroom so that a lane settles after its first picture
+        TRY(grow_checked(s.d_blocks, s.cap_blocks, size_t(n), s.st, 1));
+        static thread_local BucketScratch scratch;
+        const int bad = bucket_blocks(f->blocks, n, s.h_blocks, local.first, local.count, scratch);
+        if (bad) {
+            char idx[32];
+            snprintf(idx, sizeof(idx), "%d", bad - 1);
+            svtgpu_set_error("%s%s (line %d)", "invalid SvtGpuBlock at index ", idx, __LINE__);
+            return SVTGPU_ERR_ARG;
+        }
+        for (int i = 0; i < n; ++i) {
+            const SvtGpuBlock& b = f->blocks[i];
+            if (b.bit_depth != f->bit_depth) return SVTGPU_ERR_ARG;
+            // one bad descriptor must not make the kernel read or write outside this lane's buffers
+            const size_t w = size_t(kTxW[b.tx_size]), h = size_t(kTxH[b.tx_size]);
+            const bool bad_res = !diff && size_t(b.res_off) + (h - 1) * b.res_stride + w > f->residual_elems;
+            const bool bad_pix = (inv || diff) && size_t(b.rec_off) + (h - 1) * b.rec_stride + w > f->pixel_elems;
+            const bool bad_cf = f->qcoeff && size_t(b.coeff_off) + size_t(max_eob(b.tx_size)) > f->coeff_elems;
+            if (bad_res || bad_pix || bad_cf) {
+                char idx[32];
+                snprintf(idx, sizeof(idx), "%d", i);
+                svtgpu_set_error("%s%s (line %d)", "a block reaches beyond residual_elems / pixel_elems / coeff_elems: index ", idx, __LINE__);
+                return SVTGPU_ERR_ARG;
+            }
+            local.max_qrow = b.qrow > local.max_qrow ? b.qrow : local.max_qrow;
+            local.uses_qm |= (b.flags & SVTGPU_BLK_USE_QM) != 0;
+            if (b.flags & SVTGPU_BLK_USE_QM) local.qm_sizes[b.plane > 0] |= 1u << b.tx_size;
+            local.any_clamp16 |= (b.flags & SVTGPU_BLK_CLAMP16) != 0;
+        }
+        local.d_blocks = s.d_blocks;
+        local.bd_uniform = f->bit_depth;  // checked per block above
+        plan = &local;
     }
-    // per-block buffers are small (32 + 26 bytes per block) and the block count of a picture moves
-    // with its partitioning: 2x headroom so that a lane settles after its first picture
-    TRY(grow(s.d_blocks, s.cap_blocks, size_t(n), s.st, 1));
-    static thread_local BucketScratch scratch;
-    const int bad = bucket_blocks(f->blocks, n, s.h_blocks, plan.first, plan.count, scratch);
-    if (bad) {
-        char idx[32];
-        snprintf(idx, sizeof(idx), "%d", bad - 1);
-        svtgpu_set_error("%s%s (line %d)", "invalid SvtGpuBlock at index ", idx, __LINE__);
-        return SVTGPU_ERR_ARG;
-    }
-    for (int i = 0; i < n; ++i) {
-        const SvtGpuBlock& b = f->blocks[i];
-        if (b.bit_depth != f->bit_depth) return SVTGPU_ERR_ARG;
-        plan.max_qrow = b.qrow > plan.max_qrow ? b.qrow : plan.max_qrow;
-        plan.uses_qm |= (b.flags & SVTGPU_BLK_USE_QM) != 0;
-        plan.any_clamp16 |= (b.flags & SVTGPU_BLK_CLAMP16) != 0;
-    }
-    plan.d_blocks = s.d_blocks;
-    plan.bd_uniform = f->bit_depth;  // checked per block above
 
     const size_t px = f->bit_depth == 8 ? 1 : 2;
-    if (!diff) TRY(grow(s.d_res, s.cap_res, f->residual_elems, s.st));
+    if (!diff) TRY(grow_checked(s.d_res, s.cap_res, f->residual_elems, s.st));
     if (diff) {
         char* sp = static_cast<char*>(s.d_src);
-        TRY(grow(sp, s.cap_src, f->pixel_elems * px, s.st));
+        const int rc = grow_checked(sp, s.cap_src, f->pixel_elems * px, s.st);
         s.d_src = sp;
+        TRY(rc);
     }
     if (inv || diff) {
         char* pix = static_cast<char*>(s.d_pix);
-        TRY(grow(pix, s.cap_pix, f->pixel_elems * px, s.st));
+        const int rc = grow_checked(pix, s.cap_pix, f->pixel_elems * px, s.st);
         s.d_pix = pix;
+        TRY(rc);
     }
-    {
-        size_t cap2 = s.cap_coeff;
-        TRY(grow(s.d_q, s.cap_coeff, f->coeff_elems, s.st));
-        TRY(grow(s.d_dq, cap2, f->coeff_elems, s.st));
-        size_t cap_e = s.cap_n, cap_d = s.cap_n;
-        TRY(grow(s.d_eob, s.cap_n, size_t(n), s.st, 1));
-        TRY(grow(s.d_energy, cap_e, size_t(n), s.st, 1));
-        if (cap_d) cap_d = cap_d * 2;  // d_dist holds two values per block
-        TRY(grow(s.d_dist, cap_d, size_t(n) * 2, s.st, 1));
-    }
+    // every buffer carries its own capacity: a failed allocation leaves that one buffer empty
+    // (pointer null, capacity 0) and the next submission simply tries again
+    if (f->qcoeff) TRY(grow_checked(s.d_q, s.cap_q, f->coeff_elems, s.st));
+    if (f->dqcoeff) TRY(grow_checked(s.d_dq, s.cap_dq, f->coeff_elems, s.st));
+    TRY(grow_checked(s.d_eob, s.cap_eob, size_t(n), s.st, 1));
+    TRY(grow_checked(s.d_energy, s.cap_energy, size_t(n), s.st, 1));
+    if (f->dist) TRY(grow_checked(s.d_dist, s.cap_dist, size_t(n) * 2, s.st, 1));
 
-    CK(cudaMemcpyAsync(s.d_blocks, s.h_blocks, size_t(n) * sizeof(DevBlock), cudaMemcpyHostToDevice, s.st));
+    if (plan == &local)
+        CK(cudaMemcpyAsync(s.d_blocks, s.h_blocks, size_t(n) * sizeof(DevBlock), cudaMemcpyHostToDevice, s.st));
     if (diff) CK(cudaMemcpyAsync(s.d_src, f->src, f->pixel_elems * px, cudaMemcpyHostToDevice, s.st));
     else CK(cudaMemcpyAsync(s.d_res, f->residual, f->residual_elems * sizeof(int16_t), cudaMemcpyHostToDevice, s.st));
     if (inv || diff) CK(cudaMemcpyAsync(s.d_pix, f->pred, f->pixel_elems * px, cudaMemcpyHostToDevice, s.st));
@@ -150,7 +203,7 @@ extern "C" int svtgpu_submit_host(SvtGpuContext* c, const SvtGpuHostFrame* f, in
     b.energy = s.d_energy;
     b.src = s.d_src;
     b.dist = f->dist ? s.d_dist : nullptr;
-    TRY(svtgpu_run_internal(c, &plan, &b, stages, s.st));
+    TRY(svtgpu_run_internal(c, plan, &b, stages, s.st));
 
     if (f->qcoeff)
         CK(cudaMemcpyAsync(f->qcoeff, s.d_q, f->coeff_elems * sizeof(int32_t), cudaMemcpyDeviceToHost, s.st));

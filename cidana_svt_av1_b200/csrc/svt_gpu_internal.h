@@ -26,18 +26,23 @@ struct HostSlot {
     int ticket = -1;
     svt::DevBlock* d_blocks = nullptr;
     svt::DevBlock* h_blocks = nullptr;  // page-locked
+    size_t cap_hblocks = 0;
     size_t cap_blocks = 0;
     int16_t* d_res = nullptr;
     size_t cap_res = 0;
     void* d_pix = nullptr;  // prediction in, reconstruction out (in place)
     size_t cap_pix = 0;     // bytes
+    // one capacity per buffer: a failed allocation can only leave ITS buffer empty
     int32_t* d_q = nullptr;
+    size_t cap_q = 0;
     int32_t* d_dq = nullptr;
-    size_t cap_coeff = 0;
+    size_t cap_dq = 0;
     uint16_t* d_eob = nullptr;
+    size_t cap_eob = 0;
     uint64_t* d_energy = nullptr;
+    size_t cap_energy = 0;
     uint64_t* d_dist = nullptr;
-    size_t cap_n = 0;
+    size_t cap_dist = 0;
     void* d_src = nullptr;  // source pixels (SVTGPU_STAGE_RESIDUAL)
     size_t cap_src = 0;     // bytes
 };
@@ -71,8 +76,11 @@ struct SvtGpuPlan {
     int count[19] = {};
     uint32_t max_qrow = 0;
     bool uses_qm = false;
+    uint32_t qm_sizes[2] = {};  // [plane > 0]: bit s = some USE_QM block of tx_size s
     bool any_clamp16 = false;
     int bd_uniform = 0;  // 8 / 10 when every block has that bit depth (selects the compiled-in pixel type)
+    // extents the block list reaches (elements): what a host frame must provide
+    size_t need_res = 0, need_pix = 0, need_coeff = 0;
 };
 
 #include <atomic>

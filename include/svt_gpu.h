@@ -68,7 +68,7 @@ typedef struct SvtGpuBuffers {
     const int32_t *coeff_in; /* input of QUANT / INV when STAGE_FWD is not requested */
     int32_t *coeff;          /* optional output: transform coefficients, packed to min(w,32) */
     int32_t *qcoeff;         /* STAGE_QUANT outputs */
-    int32_t *dqcoeff;
+    int32_t *dqcoeff;        /* optional (NULL: not written; the inverse stage does not need it) */
     uint16_t *eob;           /* [n_blocks], indexed like the caller's block list */
     uint64_t *energy;        /* [n_blocks] three_quad_energy (0 unless a 64-point size) */
     /* SURVEY 8f-1, what mode decision consumes (EbFullLoop.c:763-835): */
@@ -175,7 +175,14 @@ typedef struct SvtGpuHostFrame {
     uint64_t *energy;        /* n_blocks out, or NULL */
     const void *src;         /* SVTGPU_STAGE_RESIDUAL: pixel_elems source pixels (residual unused) */
     uint64_t *dist;          /* optional n_blocks x 2 out (see SvtGpuBuffers.dist); qcoeff / dqcoeff
-                              * may then be NULL: nothing is computed for or copied into them */
+                              * may then be NULL: nothing is computed for or copied into them.
+                              * dqcoeff alone may also be NULL (what the encode pass consumes is
+                              * qcoeff + eob + recon: EbCodingLoop.c:697-731 feeds recon_coeff only
+                              * to the inverse transform, which runs here anyway) */
+    const SvtGpuPlan *plan;  /* optional: a plan made once with svtgpu_plan_create for this exact block
+                              * list (same context).  `blocks` is then ignored: nothing is validated,
+                              * sorted or uploaded per submission -- the per-picture host cost of a
+                              * caller whose partitioning repeats (a fixed geometry, a benchmark) */
 } SvtGpuHostFrame;
 /* returns immediately after queueing; *ticket (optional) identifies the submission */
 int svtgpu_submit_host(SvtGpuContext *ctx, const SvtGpuHostFrame *frame, int stages, int *ticket);

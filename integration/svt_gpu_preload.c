@@ -180,12 +180,10 @@ void av1_quantize_inv_quantize(PictureControlSet_t *picture_control_set_ptr, int
         return;
     }
     /* The accessor: the only thing the reference needs the PictureControlSet for
-     * (av1_quantize_inv_quantize_ii, EbFullLoop.c:546-613).  8-bit reads the *Md tables.  For
-     * COMPONENT_CHROMA_CB the reference fills in only quant / dequant and leaves the other rows
-     * to whatever the previous call left in the local (:568-572); the rows of the same plane
-     * are passed here, which is the same data whenever the chroma delta-q values are 0 (they
-     * always are in this encoder: av1_build_quantizer is called with zeros,
-     * EbModeDecisionConfigurationProcess.c). */
+     * (av1_quantize_inv_quantize_ii, EbFullLoop.c:548-613): with bit_increment == 0 all seven rows
+     * of the plane come from quantsMd / deqMd (the 8-bit tables mode decision uses, also inside a
+     * 10-bit encode: EbFullLoop.c:1637 calls chroma with BIT_INCREMENT_8BIT), otherwise from
+     * quants / deq (built at encoder_bit_depth, EbModeDecisionConfigurationProcess.c:2176-2202). */
     const PictureParentControlSet_t *p = picture_control_set_ptr->parent_pcs_ptr;
     const uint32_t q = p->base_qindex;
     const Quants *qs = bit_increment ? &p->quants : &p->quantsMd;
@@ -196,11 +194,10 @@ void av1_quantize_inv_quantize(PictureControlSet_t *picture_control_set_ptr, int
         shift = qs->y_quant_shift[q]; deq = dq->y_dequant_QTX[q];
     } else if (component_type == COMPONENT_CHROMA_CB) {
         zbin = qs->u_zbin[q]; round = qs->u_round[q]; quant = qs->u_quant[q];
-        shift = qs->u_quant_shift[q]; deq = p->deq.u_dequant_QTX[q];
+        shift = qs->u_quant_shift[q]; deq = dq->u_dequant_QTX[q];
     } else {
-        qs = &p->quants;
         zbin = qs->v_zbin[q]; round = qs->v_round[q]; quant = qs->v_quant[q];
-        shift = qs->v_quant_shift[q]; deq = p->deq.v_dequant_QTX[q];
+        shift = qs->v_quant_shift[q]; deq = dq->v_dequant_QTX[q];
     }
     __atomic_fetch_add(&g_calls[1], 1, __ATOMIC_RELAXED);
     p_quant(zbin, round, quant, shift, deq, coeff, quant_coeff, recon_coeff, txsize, eob,

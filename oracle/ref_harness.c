@@ -180,10 +180,14 @@ typedef struct RefBlock {
     uint32_t flags;
 } RefBlock;
 
-/* tables: [nrows][5][8] int16: zbin, round, quant, quant_shift, dequant */
-void ref_fused_blocks(const RefBlock *blk, int first, int last, int16_t *residual, void *recon,
-                      const int16_t *tables, int32_t *qcoeff, int32_t *dqcoeff, uint16_t *eob,
-                      uint64_t *energy) {
+/* tables: [nrows][5][8] int16: zbin, round, quant, quant_shift, dequant.
+ * wt / iwt / off ([2][19], -1 = none): optional quantization matrices; a 10-bit block flagged
+ * USE_QM (flags & 2) then goes through highbd_quantize_b_helper_c, the function the reference's
+ * facade picks when both matrix pointers are set (EbFullLoop.c:421-489); everything else through
+ * the RTCD pointer of its bit depth. */
+static void ref_fused_range(const RefBlock *blk, int first, int last, int16_t *residual, void *recon,
+                            const int16_t *tables, int32_t *qcoeff, int32_t *dqcoeff, uint16_t *eob,
+                            uint64_t *energy, const uint8_t *wt, const uint8_t *iwt, const int32_t *off) {
     int32_t coeff[32 * 32 * 4] __attribute__((aligned(32)));
     for (int i = first; i < last; ++i) {
         const RefBlock *b = &blk[i];
@@ -191,9 +195,10 @@ void ref_fused_blocks(const RefBlock *blk, int first, int last, int16_t *residua
         const int16_t *t = tables + (size_t)b->qrow * 40;
         ref_estimate_transform(residual + b->res_off, b->res_stride, coeff, b->tx_size,
                                b->tx_type, b->bd, &energy[i]);
+        const int o = (wt && (b->flags & 2) && b->bd != 8) ? off[(b->plane > 0) * 19 + b->tx_size] : -1;
         ref_quantize(coeff, n, t, t + 8, t + 16, t + 24, t + 32, qcoeff + b->coeff_off,
-                     dqcoeff + b->coeff_off, &eob[i], b->tx_size, b->tx_type, b->bd, 0, NULL,
-                     NULL);
+                     dqcoeff + b->coeff_off, &eob[i], b->tx_size, b->tx_type, b->bd, o >= 0 ? 1 : 0,
+                     o >= 0 ? wt + o : NULL, o >= 0 ? iwt + o : NULL);
         if (eob[i]) {
             void *dst = b->bd == 8 ? (void *)((uint8_t *)recon + b->rec_off)
                                    : (void *)((uint16_t *)recon + b->rec_off);
@@ -201,6 +206,100 @@ void ref_fused_blocks(const RefBlock *blk, int first, int last, int16_t *residua
                                     b->tx_type, b->bd, eob[i]);
         }
     }
+}
+void ref_fused_blocks(const RefBlock *blk, int first, int last, int16_t *residual, void *recon,
+                      const int16_t *tables, int32_t *qcoeff, int32_t *dqcoeff, uint16_t *eob,
+                      uint64_t *energy) {
+    ref_fused_range(blk, first, last, residual, recon, tables, qcoeff, dqcoeff, eob, energy, NULL, NULL, NULL);
+}
+
+/* ---- persistent worker pool: the timed CPU arm of bench.py ------------------------------------
+ * Workers are created once and park on a condition variable between passes; inside a pass they
+ * pull chunks of POOL_CHUNK consecutive blocks from a shared counter, so the pass is balanced
+ * whatever the mix of sizes (the 32x16 / 16x32 DCT goes through the C path and is ~3x slower
+ * per sample than its neighbours).  ref_pool_run returns the wall time of the pass in seconds,
+ * measured here, not in the caller's interpreter. */
+#include <pthread.h>
+#include <time.h>
+#define POOL_MAX 256
+#define POOL_CHUNK 64
+typedef struct PoolJob {
+    const RefBlock *blk; int n;
+    int16_t *residual; void *recon; const int16_t *tables;
+    int32_t *q, *dq; uint16_t *eob; uint64_t *energy;
+    const uint8_t *wt, *iwt; const int32_t *off;
+} PoolJob;
+static struct {
+    pthread_t th[POOL_MAX];
+    int n;
+    pthread_mutex_t mu;
+    pthread_cond_t go, done;
+    unsigned long gen;
+    int pending, stop;
+    volatile int next;
+    PoolJob job;
+} g_pool = { .mu = PTHREAD_MUTEX_INITIALIZER, .go = PTHREAD_COND_INITIALIZER, .done = PTHREAD_COND_INITIALIZER };
+
+static void pool_drain(const PoolJob *j) {
+    for (;;) {
+        const int a = __atomic_fetch_add(&g_pool.next, POOL_CHUNK, __ATOMIC_RELAXED);
+        if (a >= j->n) break;
+        const int b = a + POOL_CHUNK < j->n ? a + POOL_CHUNK : j->n;
+        ref_fused_range(j->blk, a, b, j->residual, j->recon, j->tables, j->q, j->dq, j->eob, j->energy,
+                        j->wt, j->iwt, j->off);
+    }
+}
+static void *pool_worker(void *arg) {
+    unsigned long seen = 0;
+    (void)arg;
+    for (;;) {
+        pthread_mutex_lock(&g_pool.mu);
+        while (g_pool.gen == seen && !g_pool.stop) pthread_cond_wait(&g_pool.go, &g_pool.mu);
+        if (g_pool.stop) { pthread_mutex_unlock(&g_pool.mu); return NULL; }
+        seen = g_pool.gen;
+        const PoolJob j = g_pool.job;
+        pthread_mutex_unlock(&g_pool.mu);
+        pool_drain(&j);
+        pthread_mutex_lock(&g_pool.mu);
+        if (--g_pool.pending == 0) pthread_cond_signal(&g_pool.done);
+        pthread_mutex_unlock(&g_pool.mu);
+    }
+}
+/* threads = total threads working on a pass (the caller's thread is one of them) */
+int ref_pool_start(int threads) {
+    if (threads < 1) threads = 1;
+    if (threads > POOL_MAX) threads = POOL_MAX;
+    if (g_pool.n == threads - 1 && !g_pool.stop) return threads;
+    pthread_mutex_lock(&g_pool.mu);
+    g_pool.stop = 1;
+    pthread_cond_broadcast(&g_pool.go);
+    pthread_mutex_unlock(&g_pool.mu);
+    for (int i = 0; i < g_pool.n; ++i) pthread_join(g_pool.th[i], NULL);
+    g_pool.stop = 0;
+    g_pool.n = 0;
+    for (int i = 0; i < threads - 1; ++i)
+        if (pthread_create(&g_pool.th[g_pool.n], NULL, pool_worker, NULL) == 0) ++g_pool.n;
+    return g_pool.n + 1;
+}
+double ref_pool_run(const RefBlock *blk, int n, int16_t *residual, void *recon, const int16_t *tables,
+                    int32_t *qcoeff, int32_t *dqcoeff, uint16_t *eob, uint64_t *energy,
+                    const uint8_t *wt, const uint8_t *iwt, const int32_t *off) {
+    struct timespec t0, t1;
+    const PoolJob j = { blk, n, residual, recon, tables, qcoeff, dqcoeff, eob, energy, wt, iwt, off };
+    clock_gettime(CLOCK_MONOTONIC, &t0);
+    pthread_mutex_lock(&g_pool.mu);
+    g_pool.job = j;
+    g_pool.next = 0;
+    g_pool.pending = g_pool.n;
+    ++g_pool.gen;
+    pthread_cond_broadcast(&g_pool.go);
+    pthread_mutex_unlock(&g_pool.mu);
+    pool_drain(&j);
+    pthread_mutex_lock(&g_pool.mu);
+    while (g_pool.pending) pthread_cond_wait(&g_pool.done, &g_pool.mu);
+    pthread_mutex_unlock(&g_pool.mu);
+    clock_gettime(CLOCK_MONOTONIC, &t1);
+    return (double)(t1.tv_sec - t0.tv_sec) + 1e-9 * (double)(t1.tv_nsec - t0.tv_nsec);
 }
 
 /* ---- table dumps (fixtures for tests/golden) ---- */

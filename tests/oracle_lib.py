@@ -181,9 +181,16 @@ def run_oracle_md(batch, tables, scans, clamp16=0, threads=1, inverse=True):
     return dict(qcoeff=q, dqcoeff=dq, eob=eob, energy=energy, recon=recon, dist=dist)
 
 
-def run_ref(batch, tables, threads=1, first=0, last=None, asm=1):
-    """The compiled reference (AVX2 RTCD table) over the same arrays; no qmatrix, no clamp16."""
-    import threading
+def _pool(R, threads):
+    R.ref_pool_start.restype = ctypes.c_int
+    R.ref_pool_run.restype = ctypes.c_double
+    return R.ref_pool_start(int(threads))
+
+
+def run_ref(batch, tables, threads=1, first=0, last=None, asm=1, qm=None):
+    """The compiled reference (AVX2 RTCD table) over the same arrays, on the harness's persistent
+    worker pool.  qm = (wt, iwt, off): 10-bit blocks flagged USE_QM use highbd_quantize_b_helper_c
+    with the matrices (what the reference's facade does when both pointers are set).  No clamp16."""
     R = ref(asm)
     n = batch.n_blocks
     last = n if last is None else last
@@ -193,29 +200,24 @@ def run_ref(batch, tables, threads=1, first=0, last=None, asm=1):
     energy = np.zeros(n, np.uint64)
     recon = aligned_copy(batch.pred)
     residual = aligned_copy(batch.residual)
-    blocks = np.ascontiguousarray(batch.blocks)
-
-    def work(a, b):
-        R.ref_fused_blocks(P(blocks), a, b, P(residual), P(recon), P(tables), P(q), P(dq), P(eob),
-                           P(energy))
-    sl = [(first + a, first + b) for a, b in _slices(last - first, threads)]
-    if threads == 1:
-        work(*sl[0])
-    else:
-        th = [threading.Thread(target=work, args=x) for x in sl]
-        [t.start() for t in th]
-        [t.join() for t in th]
+    blocks = np.ascontiguousarray(batch.blocks[first:last])
+    wt, iwt, off = (np.ascontiguousarray(x) for x in qm) if qm is not None else (None, None, None)
+    _pool(R, threads)
+    R.ref_pool_run(P(blocks), len(blocks), P(residual), P(recon), P(tables), P(q), P(dq), P(eob[first:last]),
+                   P(energy[first:last]), P(wt), P(iwt), P(off))
     return dict(qcoeff=q, dqcoeff=dq, eob=eob, energy=energy, recon=recon)
 
 
 class CpuRunner:
     """Pre-allocated, repeatable CPU pass over a batch for timing (bench.py cpu_baseline and
-    --impl reference).  kind 'reference' = oracle/_ref (the reference's AVX2 RTCD path),
-    'port' = oracle/svt_oracle.c.  recon is updated in place pass after pass (same work)."""
+    --impl reference).  kind 'reference' = oracle/_ref: the reference's AVX2 RTCD path (plus its
+    highbd_quantize_b_helper_c for qmatrix blocks) on the harness's persistent pthread pool, which
+    also takes the time; 'port' = oracle/svt_oracle.c on Python threads (only when oracle/_ref
+    was never built).  recon is updated in place pass after pass (same work)."""
 
     def __init__(self, batch, tables, scans=None, qm=None, kind=None):
         if kind is None:
-            kind = "reference" if (ref() is not None and qm is None) else "port"
+            kind = "reference" if ref() is not None else "port"
         self.kind, self.batch, self.qm = kind, batch, qm
         self.tables = np.ascontiguousarray(tables)
         n = batch.n_blocks
@@ -226,6 +228,7 @@ class CpuRunner:
         self.recon = aligned_copy(batch.pred)
         self.residual = aligned_copy(batch.residual)
         self.blocks = np.ascontiguousarray(batch.blocks)
+        self.qm_arrays = tuple(np.ascontiguousarray(x) for x in qm) if qm is not None else (None, None, None)
         if kind == "port":
             self.ptrs = (ctypes.c_void_p * (19 * 3))()
             self.keep = []
@@ -235,26 +238,37 @@ class CpuRunner:
                     self.keep.append(a)
                     self.ptrs[s * 3 + c] = a.ctypes.data
 
-    def _work(self, a, b):
-        if self.kind == "reference":
-            ref(1).ref_fused_blocks(P(self.blocks), a, b, P(self.residual), P(self.recon), P(self.tables),
-                                    P(self.q), P(self.dq), P(self.eob), P(self.energy))
-        else:
-            wt, iwt, off = self.qm if self.qm is not None else (None, None, None)
-            oracle().svto_fused_blocks(P(self.blocks), a, b, P(self.residual), P(self.recon),
-                                       P(self.tables), P(self.q), P(self.dq), P(self.eob), P(self.energy),
-                                       self.ptrs, 0, P(wt), P(iwt), P(off))
+    def reset(self):
+        """Prediction back in `recon`: the next pass is a fresh one (its outputs are the reference
+        results for the batch, what the parity gate of bench.py compares with)."""
+        self.recon[...] = self.batch.pred
 
-    def run(self, threads):
-        """One pass; returns seconds."""
+    def outputs(self):
+        return dict(qcoeff=self.q, dqcoeff=self.dq, eob=self.eob, energy=self.energy, recon=self.recon)
+
+    def _work(self, a, b):
+        wt, iwt, off = self.qm_arrays
+        oracle().svto_fused_blocks(P(self.blocks), a, b, P(self.residual), P(self.recon),
+                                   P(self.tables), P(self.q), P(self.dq), P(self.eob), P(self.energy),
+                                   self.ptrs, 0, P(wt), P(iwt), P(off))
+
+    def run(self, threads, n_blocks=None):
+        """One pass over the first n_blocks blocks (default: all); returns seconds."""
         import threading
         import time
+        n = len(self.blocks) if n_blocks is None else int(n_blocks)
+        if self.kind == "reference":
+            R = ref(1)
+            _pool(R, threads)
+            wt, iwt, off = self.qm_arrays
+            return float(R.ref_pool_run(P(self.blocks), n, P(self.residual), P(self.recon), P(self.tables),
+                                        P(self.q), P(self.dq), P(self.eob), P(self.energy), P(wt), P(iwt), P(off)))
         # balance by samples, not block count
-        area = np.array(TX_W)[self.blocks["tx_size"]] * np.array(TX_H)[self.blocks["tx_size"]]
+        area = np.array(TX_W)[self.blocks["tx_size"][:n]] * np.array(TX_H)[self.blocks["tx_size"][:n]]
         cum = np.cumsum(area)
         cuts = [0] + [int(np.searchsorted(cum, cum[-1] * (i + 1) / threads)) + 1 for i in range(threads - 1)]
-        cuts.append(len(self.blocks))
-        cuts = sorted(set(min(c, len(self.blocks)) for c in cuts))
+        cuts.append(n)
+        cuts = sorted(set(min(c, n) for c in cuts))
         th = [threading.Thread(target=self._work, args=(cuts[i], cuts[i + 1])) for i in range(len(cuts) - 1)]
         t0 = time.perf_counter()
         [t.start() for t in th]

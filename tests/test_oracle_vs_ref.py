@@ -254,3 +254,29 @@ def test_tu_distortion(asm):
             R.ref_tu_distortion(P(cf), P(dq), s, eob, u64(energy), P(a), asm)
             O.svto_tu_distortion(P(cf), P(dq), s, eob, u64(energy), P(b))
             assert np.array_equal(a, b), (s, amp, eob, a, b)
+
+
+@pytest.mark.parametrize("bd,use_qm", [(8, False), (10, False), (10, True)])
+def test_pool_frame_batch_equals_the_restatement(bd, use_qm):
+    """The harness's pthread pool (bench.py's CPU arm and the checker of its parity gate) over a
+    mixed-size frame batch == the plain-C restatement, including the qmatrix routing; the
+    reference skips the inverse when eob == 0, which leaves the prediction in place either way."""
+    from cidana_svt_av1_b200 import workloads as wl
+    from golden_util import load_qmatrices, load_quant_tables, load_scans
+    from oracle_lib import CpuRunner, build_tables, qm_pack, run_oracle, run_ref
+    batch = wl.make_frame_batch(256, 192, 2, bd, seed=91, qindex=100, laplace_b=20.0, use_qm=use_qm)
+    qt = load_quant_tables()
+    tables = build_tables({p: qt[(bd, p)] for p in range(3)})
+    qm = qm_pack(load_qmatrices(), 6) if use_qm else None
+    want = run_oracle(batch, tables, load_scans(), qm=qm, threads=4)
+    for threads in (1, 5):
+        got = run_ref(batch, tables, threads=threads, qm=qm)
+        for k in ("qcoeff", "dqcoeff", "eob", "energy", "recon"):
+            assert np.array_equal(got[k], want[k]), (k, threads)
+    r = CpuRunner(batch, tables, scans=load_scans(), qm=qm)
+    assert r.kind == "reference"
+    assert r.run(3) > 0
+    r.reset()
+    r.run(3)
+    for k, v in r.outputs().items():
+        assert np.array_equal(v, want[k]), k

@@ -22,14 +22,15 @@ ap.add_argument("--h", type=int, default=1080)
 ap.add_argument("--frames", type=int, default=10)
 ap.add_argument("--qp", type=int, default=30)
 ap.add_argument("--level", default="AB")
+ap.add_argument("--bd", type=int, default=8)
 a = ap.parse_args()
 with tempfile.TemporaryDirectory() as d:
     clip, ref, gpu = (os.path.join(d, n) for n in ("clip.yuv", "ref.ivf", "gpu.ivf"))
-    e2e.make_clip(clip, a.w, a.h, a.frames)
-    t_ref, _ = e2e.encode(clip, ref, a.w, a.h, a.frames, a.qp, timeout=3600)
-    t_gpu, log = e2e.encode(clip, gpu, a.w, a.h, a.frames, a.qp, gpu_level=a.level, timeout=3600)
+    e2e.make_clip(clip, a.w, a.h, a.frames, bd=a.bd)
+    t_ref, _ = e2e.encode(clip, ref, a.w, a.h, a.frames, a.qp, timeout=3600, bd=a.bd)
+    t_gpu, log = e2e.encode(clip, gpu, a.w, a.h, a.frames, a.qp, gpu_level=a.level, timeout=3600, bd=a.bd)
     same = open(ref, "rb").read() == open(gpu, "rb").read()
-    print(json.dumps({"clip": f"{a.w}x{a.h} 4:2:0 8-bit, {a.frames} frames, synthetic", "enc_mode": 8, "qp": a.qp,
+    print(json.dumps({"clip": f"{a.w}x{a.h} 4:2:0 {a.bd}-bit, {a.frames} frames, synthetic", "enc_mode": 8, "qp": a.qp,
                       "level": a.level, "reference_s": round(t_ref, 2), "gpu_path_s": round(t_gpu, 2),
                       "ivf_bytes": os.path.getsize(ref), "ivf_md5": e2e.md5(ref), "byte_identical": same,
                       "preload_log": [l for l in log.splitlines() if "svtgpu" in l]}))
