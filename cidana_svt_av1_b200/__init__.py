@@ -6,9 +6,9 @@ include/svt_gpu.h); this package is the thin host-side mirror of the reference i
 There is no CPU fallback: importing works anywhere, but every compute call needs the CUDA
 library and a B200 and raises loudly otherwise.
 """
-from .api import (SvtGpu, SvtGpuError, av1_estimate_transform, av1_inv_transform_recon,  # noqa: F401
+from .api import (SvtGpu, SvtGpuError, SvtGpuMulti, av1_estimate_transform, av1_inv_transform_recon,  # noqa: F401
                   av1_inv_transform_recon8bit, av1_quantize_inv_quantize, lib, load_library)
 from . import workloads  # noqa: F401
 
-__all__ = ["SvtGpu", "SvtGpuError", "lib", "load_library", "workloads", "av1_estimate_transform",
+__all__ = ["SvtGpu", "SvtGpuError", "SvtGpuMulti", "lib", "load_library", "workloads", "av1_estimate_transform",
            "av1_quantize_inv_quantize", "av1_inv_transform_recon", "av1_inv_transform_recon8bit"]

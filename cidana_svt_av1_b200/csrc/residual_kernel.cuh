@@ -239,18 +239,19 @@ struct Geo {
     // 74 us at 5 CTAs, 8x8: 58 vs 67 us at 8; 32x32: 56 us at 3 vs 60 us at 2)
     static constexpr int CTAS_PER_SM =
         cmin((cmax(W, H) >= 64 ? 2 : (cmax(W, H) >= 32 ? 3 : (cmax(W, H) >= 16 ? 4 : SVT_OCC8))) * 256 / NT,
-             cmax(1, (228 * 1024) / (SMEM_BYTES + 1024 + 104 * NB)));
+             cmax(1, (228 * 1024) / (SMEM_BYTES + 1024 + 108 * NB)));
 };
 
 struct QSet { int zbin, round, quant, qshift, dequant; };  // one of {DC, AC}
 struct QRow { QSet dc, ac; };  // zbin / round already scaled by log_scale
 template <int NB>
-struct CtaShared {  // small per-CTA state next to the buffers above (104 bytes per block)
+struct CtaShared {  // small per-CTA state next to the buffers above (108 bytes per block)
     DevBlock blk[NB];
     QRow q[NB];  // this block's quantizer row, pre-scaled
     int eob[NB];
     unsigned long long energy[NB];
     unsigned long long dist[NB][2];  // sum (coeff - dq)^2, sum coeff^2 over the coded region
+    int fast[NB];  // the block is inside fast_limit: its inverse transform runs without clamps
 };
 
 // read-only global load through L1 (LDG.CONSTANT on the device)
@@ -451,8 +452,10 @@ SVT_HD QRow load_qrow(const int16_t* t) {
 // highbd_quantize_b_helper_c (EbFullLoop.c:239) for the tables av1_build_quantizer produces.
 // Branch-free: the level is computed for every position and zeroed below zbin.  t1max is 32767
 // for the 8-bit C variant (EbFullLoop.c:86-88) and INT_MAX otherwise.  Returns |level|.
+// asum: running sum of |dqcoeff| (the bound that lets the inverse transform drop its clamps, see
+// fast_limit below)
 template <int LOG_SCALE>
-SVT_HD int quant_flat(int cf, const QSet& q, int t1max, int& qc, int& dqc) {
+SVT_HD int quant_flat(int cf, const QSet& q, int t1max, int& qc, int& dqc, unsigned& asum) {
     const int sgn = (cf >> 31) | 1;
     const int ab = cf < 0 ? -cf : cf;
     int t1 = ab + q.round;
@@ -465,15 +468,22 @@ SVT_HD int quant_flat(int cf, const QSet& q, int t1max, int& qc, int& dqc) {
     qc = int(unsigned(aq) * unsigned(sgn));
     if constexpr (LOG_SCALE == 0) {
         dqc = int(unsigned(qc) * unsigned(q.dequant));
+        asum = unsigned(aq) * unsigned(q.dequant) + asum;  // one multiply-add on the FMA pipe
     } else {
         const int adq = int(unsigned(aq) * unsigned(q.dequant)) >> LOG_SCALE;
         dqc = int(unsigned(adq) * unsigned(sgn));
+        asum += unsigned(adq);
     }
     return aq;
 }
+template <int LOG_SCALE>
+SVT_HD int quant_flat(int cf, const QSet& q, int t1max, int& qc, int& dqc) {
+    unsigned unused = 0;
+    return quant_flat<LOG_SCALE>(cf, q, t1max, qc, dqc, unused);
+}
 // with quantization matrices: highbd_quantize_b_helper_c, EbFullLoop.c:239-296
 template <int LOG_SCALE>
-SVT_HD int quant_qm(int cf, const QSet& q, int wt, int iwt, int& qc, int& dqc) {
+SVT_HD int quant_qm(int cf, const QSet& q, int wt, int iwt, int& qc, int& dqc, unsigned& asum) {
     const int sign = cf >> 31;
     const int ab = (cf ^ sign) - sign;
     const int cw = int(unsigned(cf) * unsigned(wt));
@@ -487,9 +497,40 @@ SVT_HD int quant_qm(int cf, const QSet& q, int wt, int iwt, int& qc, int& dqc) {
         const int adq = int(unsigned(aq) * unsigned(dq)) >> LOG_SCALE;
         qc = (aq ^ sign) - sign;
         dqc = (adq ^ sign) - sign;
+        asum += unsigned(adq);
     }
     return aq;
 }
+
+// ---- when the inverse transform needs no clamps ----------------------------------------------------
+// The reference clamps the input of the inverse row pass to bd + 8 bits, every add/sub of the row
+// networks to the same range, the input of the column pass to 16 bits and every add/sub of the
+// column networks to 16 bits (EbTransforms.c:8215-8291, clamp_value :5458).  None of those can
+// bind for a block whose dequantised coefficients are small in L1 norm S = sum |dqcoeff|:
+//   * every add/sub node of the inverse DCT / ADST networks is a combination sum a_i x_i of the
+//     inputs with |a_i| <= 1 (checked numerically for every size by tests/host_emul.cpp:
+//     emul_inverse_node_gain), so |node| <= sum |x_i| + E, E = accumulated half_btf rounding
+//     (0.5 per rotation, fewer than 512 rotations in the largest network);
+//   * a row's inputs are a subset of the block's coefficients (rect scaling only shrinks them), so
+//     S + E < 2^(bd+7) covers the input clamp and every row node;
+//   * a column's inputs are row outputs shifted down by inv_shift0 = s0; an identity row scales
+//     by G <= 4, the other kinds by <= 1, so a column's L1 norm is at most
+//     (G S + KH E) / 2^s0 + KH, which must stay below 2^15 - E.
+// Blocks inside the limit run the clamp-free networks (forward-transform cost: one instruction per
+// add/sub instead of two); the others run the clamped ones.  Same results by construction, and
+// both are pinned to the reference by the tests (small and full-range residuals).
+constexpr int kFastE = 512;
+SVT_HD constexpr int id_gain(int n) { return n == 4 ? 2 : (n == 8 ? 2 : (n == 16 ? 3 : 4)); }
+template <int W, int H, int KIND_ROW>
+SVT_HD constexpr unsigned fast_limit(bool bd10) {
+    constexpr int KH = cmin(H, 32), S0 = inv_shift0(W, H), G = KIND_ROW == 2 ? id_gain(W) : 1;
+    constexpr long long col = ((((32767LL - kFastE - KH) << S0) - (long long)KH * kFastE)) / G;
+    const long long row = (1LL << ((bd10 ? 10 : 8) + 7)) - 1 - kFastE;
+    return unsigned(col < row ? col : row);
+}
+// host emulation only: the decision comes from the caller (who runs the block's rows twice), and
+// the row's share of S goes back to it
+struct RowAux { unsigned sum = 0; int fast = 0; };
 
 // ---- phase 2: forward row -> (energy, pack) -> quantize -> inverse row, all on one thread's registers
 // isc: this block's iscan table (global memory).  Returns the row's eob candidate and
@@ -560,9 +601,49 @@ SVT_HD void flush_q(const KParams& p, const DevBlock& d, int r, int* row, const 
 
 // DIST: also accumulate this row's share of sum (coeff - dq)^2 and sum coeff^2 over the coded
 // region (full_distortion_kernel32_bits, EbPictureOperators.c:283-313) into dsum[0..1].
+// The inverse row pass of one row (inv_txfm2d_add_c row pass, EbTransforms.c:8215-8236), from the
+// dequantised row in x[] to the transposing store.  FAST: the block is inside fast_limit, so no
+// clamp can bind and none is executed.
+template <int W, int H, int KIND, class C, bool FAST>
+SVT_HD void inv_row_store(int (&x)[W], int* row, bool bd10) {
+    using G = Geo<W, H>;
+    constexpr int KW = G::KW;
+    const Clamp krow_c(bd10 ? 18 : 16);  // clamp_buf(bd + 8) and the row stage range: 16 / 18
+#pragma unroll
+    for (int c = 0; c < W; ++c) {
+        if (c >= KW) x[c] = 0;  // 64-wide: re-expansion with zeros, EbTransforms.c:8299
+        else {
+            if constexpr (G::RECT) x[c] = mul_round12(x[c], 2896);
+            if constexpr (!FAST) x[c] = krow_c(x[c]);
+        }
+    }
+    if constexpr (FAST) inv1d_k<W, KIND>(x, NoClamp());
+    else inv1d_k<W, KIND>(x, krow_c);
+    constexpr int IS0 = inv_shift0(W, H);
+    // clamp_buf(max(bd + 6, 16)) = 16 bits at the input of the column pass
+    // (EbTransforms.c:8241) is applied here, before the transposing store.  With 8-bit
+    // blocks it cannot bind after a DCT row (its last stage is a 16-bit clamped add/sub and
+    // round_shift only shrinks) nor after an 8/16-point ADST row followed by a shift (the
+    // sign permutation can turn -2^15 into 2^15, which the shift halves), so it is elided
+    // where the bit depth is a compile-time 8.
+    constexpr bool IN_RANGE = FAST || (C::BD_STATIC == 8 && (KIND == 0 || (KIND == 1 && W >= 8 && IS0 > 0)));
+    const Clamp k16(16);
+#pragma unroll
+    for (int c = 0; c < W; c += 4) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            if constexpr (IS0 > 0) x[c + j] = rshift<(IS0 > 0 ? IS0 : 1)>(x[c + j]);
+            if constexpr (!IN_RANGE) x[c + j] = k16(x[c + j]);
+        }
+        *reinterpret_cast<int4*>(row + c) = make_int4(x[c], x[c + 1], x[c + 2], x[c + 3]);
+    }
+}
+
+// fast_flag: the block's shared "no clamp can bind" flag (written here, read by the column pass)
 template <int W, int H, int KIND, bool QM, bool DIST, class C = CfgRuntime>
 SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int* buf, const int16_t* isc,
-                  int& eob_max, unsigned long long& energy_sum, unsigned long long (&dsum)[2]) {
+                  int& eob_max, unsigned long long& energy_sum, unsigned long long (&dsum)[2],
+                  int* fast_flag, RowAux& aux) {
     static_assert(!(QM && DIST), "the distortion outputs are built for the flat quantizer only");
     using G = Geo<W, H>;
     dsum[0] = dsum[1] = 0;
@@ -572,6 +653,7 @@ SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int
     int x[W];
     eob_max = 0;
     energy_sum = 0;
+    unsigned asum = 0;  // this row's share of S = sum |dqcoeff| (fast_limit)
     const uint32_t cbase = d.coeff_off + r * KW;
 
     if (C::stg(p) & STAGE_FWD) {
@@ -647,7 +729,7 @@ SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int
                     const int c = c0 + j;
                     int dqc;
                     const int cf = x[c];
-                    const int aq = quant_flat<LS>(cf, c == 0 ? q0 : qa, t1max, qv[j], dqc);
+                    const int aq = quant_flat<LS>(cf, c == 0 ? q0 : qa, t1max, qv[j], dqc, asum);
                     if (lvrow) lv4 |= uint32_t(aq > 127 ? 127 : aq) << (8 * j);
                     if constexpr (DIST) {
                         const int dd = cf - dqc;
@@ -674,7 +756,7 @@ SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int
                     const int c = c0 + j;
                     int dqc;
                     const int aq = quant_qm<LS>(x[c], c == 0 ? q0 : qa, int((w4 >> (8 * j)) & 255),
-                                                int((i4 >> (8 * j)) & 255), qv[j], dqc);
+                                                int((i4 >> (8 * j)) & 255), qv[j], dqc, asum);
                     if (lvrow) lv4 |= uint32_t(aq > 127 ? 127 : aq) << (8 * j);
                     x[c] = dqc;
                     last = aq != 0 ? c : last;
@@ -689,34 +771,28 @@ SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int
 
     if (C::stg(p) & STAGE_INV) {  // inv_txfm2d_add_c row pass, EbTransforms.c:8215-8236
         if (r < KH) {
-            const Clamp krow_c(bd10 ? 18 : 16);  // clamp_buf(bd + 8) and the row stage range: 16 / 18
+            // S = sum |dqcoeff| over the block: the rows of a block are LB consecutive lanes of one
+            // warp (its coded rows), so a butterfly of shuffles gives every row owner the total
+            bool fast = false;
+            if (C::stg(p) & STAGE_QUANT) {
+#if defined(__CUDA_ARCH__)
+                constexpr int LB = H < 32 ? H : 32;
+                const int lane = threadIdx.x & 31, li = r & (LB - 1);
+                const unsigned bmask = LB == 32 ? 0xffffffffu : (((1u << LB) - 1u) << (lane - li));
+                unsigned tot = asum < (1u << 24) ? asum : (1u << 24);
 #pragma unroll
-            for (int c = 0; c < W; ++c) {
-                if (c >= KW) x[c] = 0;  // 64-wide: re-expansion with zeros, EbTransforms.c:8299
-                else {
-                    if constexpr (G::RECT) x[c] = mul_round12(x[c], 2896);
-                    x[c] = krow_c(x[c]);
-                }
+                for (int m = LB / 2; m > 0; m >>= 1) tot += __shfl_xor_sync(bmask, tot, m);
+                fast = tot <= fast_limit<W, H, KIND>(bd10);
+                if (li == 0) *fast_flag = fast;
+#else
+                aux.sum = asum;
+                fast = aux.fast != 0;
+#endif
+            } else if (r == 0) {
+                *fast_flag = 0;  // inverse of caller-supplied coefficients: the clamped networks
             }
-            inv1d_k<W, KIND>(x, krow_c);
-            constexpr int IS0 = inv_shift0(W, H);
-            // clamp_buf(max(bd + 6, 16)) = 16 bits at the input of the column pass
-            // (EbTransforms.c:8241) is applied here, before the transposing store.  With 8-bit
-            // blocks it cannot bind after a DCT row (its last stage is a 16-bit clamped add/sub and
-            // round_shift only shrinks) nor after an 8/16-point ADST row followed by a shift (the
-            // sign permutation can turn -2^15 into 2^15, which the shift halves), so it is elided
-            // where the bit depth is a compile-time 8.
-            constexpr bool IN_RANGE = C::BD_STATIC == 8 && (KIND == 0 || (KIND == 1 && W >= 8 && IS0 > 0));
-            const Clamp k16(16);
-#pragma unroll
-            for (int c = 0; c < W; c += 4) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    if constexpr (IS0 > 0) x[c + j] = rshift<(IS0 > 0 ? IS0 : 1)>(x[c + j]);
-                    if constexpr (!IN_RANGE) x[c + j] = k16(x[c + j]);
-                }
-                *reinterpret_cast<int4*>(row + c) = make_int4(x[c], x[c + 1], x[c + 2], x[c + 3]);
-            }
+            if (fast) inv_row_store<W, H, KIND, C, true>(x, row, bd10);
+            else inv_row_store<W, H, KIND, C, false>(x, row, bd10);
         } else {
 #pragma unroll
             for (int c = 0; c < W; c += 4) *reinterpret_cast<int4*>(row + c) = make_int4(0, 0, 0, 0);
@@ -725,16 +801,17 @@ SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int
 }
 template <int W, int H, bool QM, bool DIST = false, class C = CfgRuntime>
 SVT_HD void phase_row(const KParams& p, const DevBlock& d, const QRow& q, int r, int* buf,
-                      const int16_t* isc, int& e, unsigned long long& en, unsigned long long (&ds)[2]) {
+                      const int16_t* isc, int& e, unsigned long long& en, unsigned long long (&ds)[2],
+                      int* fast_flag, RowAux& aux) {
     const int kind = hkind(d);
-    if constexpr (W == 64) row_k<W, H, 0, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds);
+    if constexpr (W == 64) row_k<W, H, 0, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds, fast_flag, aux);
     else if constexpr (W == 32) {
-        if (kind == 2) row_k<W, H, 2, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds);
-        else row_k<W, H, 0, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds);
+        if (kind == 2) row_k<W, H, 2, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds, fast_flag, aux);
+        else row_k<W, H, 0, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds, fast_flag, aux);
     } else {
-        if (kind == 0) row_k<W, H, 0, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds);
-        else if (kind == 1) row_k<W, H, 1, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds);
-        else row_k<W, H, 2, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds);
+        if (kind == 0) row_k<W, H, 0, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds, fast_flag, aux);
+        else if (kind == 1) row_k<W, H, 1, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds, fast_flag, aux);
+        else row_k<W, H, 2, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds, fast_flag, aux);
     }
 }
 // eob rule, three_quad_energy and scaling of the per-TU distortion (EbFullLoop.c:808-835;
@@ -753,7 +830,7 @@ SVT_HD void finish_dist(unsigned long long res, unsigned long long pred, int eob
 // ---- phase 3: inverse column transform + reconstruction on the staged prediction block --------------
 // pix: the block's prediction pixels in shared memory (dense, W per row), overwritten in place with
 // the reconstruction (highbd_clip_pixel_add + check_range, EbTransforms.c:7794-7813).
-template <int W, int H, int KIND, class PIX>
+template <int W, int H, int KIND, class PIX, bool FAST>
 SVT_HD void inv_col_k(const DevBlock& d, int c, const int* buf, PIX* pix, int pmax, int rmax) {
     using G = Geo<W, H>;
     const bool lr = d.meta & META_LR;
@@ -762,7 +839,8 @@ SVT_HD void inv_col_k(const DevBlock& d, int c, const int* buf, PIX* pix, int pm
     int x[H];
 #pragma unroll
     for (int r = 0; r < H; ++r) x[r] = src[r * G::LD];  // already clamped to 16 bits by the row pass
-    inv1d_k<H, KIND>(x, k16);
+    if constexpr (FAST) inv1d_k<H, KIND>(x, NoClamp());  // inside fast_limit: no clamp can bind
+    else inv1d_k<H, KIND>(x, k16);
     // check_range (EbTransforms.c:7794) clamps the residual to +-(2^(7+bd) - 1 + (914 << (bd-7))),
     // i.e. beyond +-34595.  It can never bind here: every 1-D inverse output is bounded by its
     // 16-bit input clamp (butterfly outputs are re-clamped to 16 bits; identity scales by <= 4;
@@ -780,23 +858,31 @@ SVT_HD void inv_col_k(const DevBlock& d, int c, const int* buf, PIX* pix, int pm
 #endif
     }
 }
-template <int W, int H, int KIND, class C = CfgRuntime>
+template <int W, int H, int KIND, class C, bool FAST>
 SVT_HD void inv_col_bd(const DevBlock& d, int c, const int* buf, void* pix) {
     if (C::bd10(d))
-        inv_col_k<W, H, KIND>(d, c, buf, static_cast<uint16_t*>(pix), 1023, (1 << 17) - 1 + (914 << 3));
+        inv_col_k<W, H, KIND, uint16_t, FAST>(d, c, buf, static_cast<uint16_t*>(pix), 1023, (1 << 17) - 1 + (914 << 3));
     else
-        inv_col_k<W, H, KIND>(d, c, buf, static_cast<uint8_t*>(pix), 255, (1 << 15) - 1 + (914 << 1));
+        inv_col_k<W, H, KIND, uint8_t, FAST>(d, c, buf, static_cast<uint8_t*>(pix), 255, (1 << 15) - 1 + (914 << 1));
 }
+// fast: the block's flag from the row pass (fast_limit); only the DCT / long ADST columns have
+// clamps to drop
 template <int W, int H, class C = CfgRuntime>
-SVT_HD void phase_inv_col(const DevBlock& d, int c, const int* buf, void* pix) {
+SVT_HD void phase_inv_col(const DevBlock& d, int c, const int* buf, void* pix, bool fast) {
     const int kind = vkind(d);
-    if constexpr (H == 64) inv_col_bd<W, H, 0, C>(d, c, buf, pix);
-    else if constexpr (H == 32) {
-        if (kind == 2) inv_col_bd<W, H, 2, C>(d, c, buf, pix); else inv_col_bd<W, H, 0, C>(d, c, buf, pix);
+    if constexpr (H == 64) {
+        if (fast) inv_col_bd<W, H, 0, C, true>(d, c, buf, pix); else inv_col_bd<W, H, 0, C, false>(d, c, buf, pix);
+    } else if constexpr (H == 32) {
+        if (kind == 2) inv_col_bd<W, H, 2, C, false>(d, c, buf, pix);
+        else if (fast) inv_col_bd<W, H, 0, C, true>(d, c, buf, pix);
+        else inv_col_bd<W, H, 0, C, false>(d, c, buf, pix);
     } else {
-        if (kind == 0) inv_col_bd<W, H, 0, C>(d, c, buf, pix);
-        else if (kind == 1) inv_col_bd<W, H, 1, C>(d, c, buf, pix);
-        else inv_col_bd<W, H, 2, C>(d, c, buf, pix);
+        if (kind == 0) {
+            if (fast) inv_col_bd<W, H, 0, C, true>(d, c, buf, pix); else inv_col_bd<W, H, 0, C, false>(d, c, buf, pix);
+        } else if (kind == 1) {
+            if (fast && H > 4) inv_col_bd<W, H, 1, C, true>(d, c, buf, pix);
+            else inv_col_bd<W, H, 1, C, false>(d, c, buf, pix);
+        } else inv_col_bd<W, H, 2, C, false>(d, c, buf, pix);
     }
 }
 
@@ -938,8 +1024,9 @@ residual_kernel(const __grid_constant__ KParams p, int first_block, int count) {
         if (b < nb) {
             int e;
             unsigned long long en, ds[2];
+            RowAux aux;
             phase_row<W, H, QM, DIST, C>(p, sh.blk[b], sh.q[b], r, buf + b * G::BLK,
-                                      block_iscan<W, H>(p, sh.blk[b]), e, en, ds);
+                                      block_iscan<W, H>(p, sh.blk[b]), e, en, ds, &sh.fast[b], aux);
             if (e) atomicMax(&sh.eob[b], e);
             if (G::KW != W || G::KH != H) { if (en) atomicAdd(&sh.energy[b], en); }
             if constexpr (DIST) {
@@ -966,7 +1053,7 @@ residual_kernel(const __grid_constant__ KParams p, int first_block, int count) {
 #pragma unroll 1
         for (int task = tid; task < G::NB * W; task += G::NT) {
             const int b = task / W, c = task % W;
-            if (b < nb) phase_inv_col<W, H, C>(sh.blk[b], c, buf + b * G::BLK, stage + b * G::SP);
+            if (b < nb) phase_inv_col<W, H, C>(sh.blk[b], c, buf + b * G::BLK, stage + b * G::SP, sh.fast[b] != 0);
         }
         sync();
         TR();

@@ -189,6 +189,30 @@ int svtgpu_submit_host(SvtGpuContext *ctx, const SvtGpuHostFrame *frame, int sta
 /* blocks until submission `ticket` (or all of them when ticket < 0) has fully landed in host memory */
 int svtgpu_wait_host(SvtGpuContext *ctx, int ticket);
 
+/* ---- several GPUs from ONE process (svtgpu_create(device_ids[], n)) -------------------
+ * For a C caller that cannot run one process per GPU (the encoder).  Pictures are independent on
+ * this path, so submission i runs on device i mod n (svtgpu_multi_device_of): whole pictures per
+ * device, no collective.  Tables are uploaded to every device; svtgpu_multi_submit_host /
+ * svtgpu_multi_wait_host are svtgpu_submit_host / svtgpu_wait_host of the chosen device's context.
+ * *ticket = the global submission index.  frame->plan, if given, must have been made on
+ * svtgpu_multi_context(m, svtgpu_multi_device_of(n, index of this submission)).  The same device
+ * id may be listed more than once (two contexts, twice the lanes, on one GPU). */
+#define SVTGPU_MAX_DEVICES 16
+typedef struct SvtGpuMulti SvtGpuMulti;
+int svtgpu_create_multi(SvtGpuMulti **multi, const int *device_ids, int n_devices);
+void svtgpu_multi_destroy(SvtGpuMulti *multi);
+int svtgpu_multi_count(const SvtGpuMulti *multi);
+SvtGpuContext *svtgpu_multi_context(SvtGpuMulti *multi, int i);
+int svtgpu_multi_device_of(int n_devices, long long submission_index); /* host only, no GPU needed */
+int svtgpu_multi_upload_quant_tables(SvtGpuMulti *multi, const int16_t *tables, int n_rows);
+int svtgpu_multi_upload_qmatrix(SvtGpuMulti *multi, const uint8_t *wt, const uint8_t *iwt, int n_bytes,
+                                const int32_t *off /* [2][19] */);
+int svtgpu_multi_submit_host(SvtGpuMulti *multi, const SvtGpuHostFrame *frame, int stages,
+                             long long *ticket);
+/* ticket < 0: every submission on every device; otherwise everything queued so far on the device
+ * that submission `ticket` went to */
+int svtgpu_multi_wait_host(SvtGpuMulti *multi, long long ticket);
+
 /* ---- allocation-free quantizer ---------------------------------------------------------------
  * No counterpart in the reference: this entry point was added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving

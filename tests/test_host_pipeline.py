@@ -129,3 +129,22 @@ def test_qmatrix_blocks_without_an_upload_are_an_error():
     want = checker(batch, qm=qm)
     for k in KEYS:
         assert np.array_equal(out[k], want[k]), k
+
+
+def test_multi_device_handle_round_robins_pictures():
+    """svtgpu_create_multi through the C ABI: every visible device (the same device twice on a
+    one-GPU box, which exercises the same bookkeeping), pictures round-robin, outputs == checker."""
+    import torch
+    n_dev = torch.cuda.device_count()
+    ids = list(range(n_dev)) if n_dev >= 2 else [0, 0]
+    batch = wl.make_frame_batch(384, 256, 7, 8, seed=12)
+    want = checker(batch)
+    m = pkg.SvtGpuMulti(ids)
+    m.upload_quant_tables(tables(8))
+    for rep in range(2):
+        out = m.run_host(batch)
+        for k in KEYS:
+            assert np.array_equal(out[k], want[k]), (rep, k)
+    m.close()
+    with pytest.raises(pkg.SvtGpuError):
+        pkg.SvtGpuMulti([0, 99])

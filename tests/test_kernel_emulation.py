@@ -225,3 +225,47 @@ def test_plan_rejects_bad_blocks():
         bad.blocks[field] = val
         with pytest.raises(AssertionError):
             run_emul(bad, tables)
+
+
+def test_inverse_networks_have_unit_node_gain():
+    """fast_limit (residual_kernel.cuh), fact 1: no add/sub node of an inverse DCT / ADST network
+    weighs any single input by more than 1, so |node| <= sum |inputs| + rounding."""
+    E = emul()
+    E.emul_inverse_node_gain.restype = ctypes.c_double
+    for kind, sizes in ((0, (4, 8, 16, 32, 64)), (1, (4, 8, 16))):
+        for n in sizes:
+            g = E.emul_inverse_node_gain(n, kind)
+            assert 0.5 < g <= 1.0 + 1e-3, (kind, n, g)
+
+
+def test_clamp_free_inverse_equals_clamped_inside_the_limit():
+    """fast_limit, fact 2: with L1 norm + kFastE inside the stage range the clamped and the
+    clamp-free networks agree on every output -- tried right at the limit, for every size and kind
+    and both stage ranges; and beyond the range they do differ somewhere (the test can fail)."""
+    E = emul()
+    e = E.emul_fast_e()
+    differs_beyond = 0
+    for kind, sizes in ((0, (4, 8, 16, 32, 64)), (1, (8, 16))):
+        for n in sizes:
+            for bits in (16, 18):
+                lim = (1 << (bits - 1)) - 1 - e
+                for l1 in (lim, lim - 1, lim // 2, 7):
+                    assert E.emul_clampfree_diff(n, kind, 17 * n + bits, l1, bits, 3000) == 0, (kind, n, bits, l1)
+                differs_beyond += E.emul_clampfree_diff(n, kind, 5, 3 * (1 << bits), bits, 3000) > 0
+    assert differs_beyond > 0
+
+
+def test_both_inverse_paths_are_exercised():
+    """The frame workloads run (almost) entirely inside fast_limit, the full-range sweep (almost)
+    entirely outside: the emulation counts which inverse a block took."""
+    E = emul()
+    blocks, fast = ctypes.c_longlong(), ctypes.c_longlong()
+    E.emul_fast_stats(ctypes.byref(blocks), ctypes.byref(fast))
+    small = wl.make_frame_batch(256, 128, 1, 8, seed=3)
+    _check(run_emul(small, _tables(8)), run_oracle(small, _tables(8), load_scans()), "frame")
+    E.emul_fast_stats(ctypes.byref(blocks), ctypes.byref(fast))
+    assert blocks.value == small.n_blocks and fast.value > 0.9 * blocks.value, (blocks.value, fast.value)
+    full = wl.make_packed_batch([(2, 0), (3, 0), (1, 5)], 8, 20, seed=4)
+    _check(run_emul(full, _tables(8)), run_oracle(full, _tables(8), load_scans()), "sweep")
+    E.emul_fast_stats(ctypes.byref(blocks), ctypes.byref(fast))
+    assert fast.value < 0.2 * blocks.value, (blocks.value, fast.value)

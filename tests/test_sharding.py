@@ -104,3 +104,21 @@ def test_two_ranks_over_gloo():
     d0 = int(np.bitwise_xor.reduce(out["qcoeff"][:n0].astype(np.int64) * 2654435761 % (1 << 31)))
     d1 = int(np.bitwise_xor.reduce(out["qcoeff"][n0:].astype(np.int64) * 2654435761 % (1 << 31)))
     assert (d0, d1) == (got[0][4], got[1][4])
+
+
+def test_multi_device_partitioning_matches_the_rank_sharding():
+    """svtgpu_create_multi round-robins pictures over its devices (host-only rule, no GPU needed):
+    every picture goes to exactly one device, loads differ by at most one picture, and with
+    world = 2 device d gets the pictures a two-rank run would give rank d under a round-robin
+    frame split."""
+    import ctypes
+    import cidana_svt_av1_b200 as pkg
+    L = pkg.load_library()
+    for world in (1, 2, 3, 8):
+        owner = [L.svtgpu_multi_device_of(world, ctypes.c_longlong(i)) for i in range(37)]
+        assert all(0 <= d < world for d in owner)
+        loads = [owner.count(d) for d in range(world)]
+        assert max(loads) - min(loads) <= 1
+        assert owner == [i % world for i in range(37)]
+    assert L.svtgpu_multi_device_of(0, ctypes.c_longlong(1)) == -1
+    assert L.svtgpu_multi_device_of(2, ctypes.c_longlong(-1)) == -1
