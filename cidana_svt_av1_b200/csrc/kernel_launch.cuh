@@ -3,6 +3,7 @@
 // for half of the 19 transform sizes; svt_gpu_api.cu only sees launch_bucket().
 #pragma once
 #include <cuda_runtime.h>
+#include <stdlib.h>
 #include "residual_kernel.cuh"
 
 namespace svt {

@@ -793,10 +793,8 @@ SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int
             }
             if (fast) inv_row_store<W, H, KIND, C, true>(x, row, bd10);
             else inv_row_store<W, H, KIND, C, false>(x, row, bd10);
-        } else {
-#pragma unroll
-            for (int c = 0; c < W; c += 4) *reinterpret_cast<int4*>(row + c) = make_int4(0, 0, 0, 0);
         }
+        // rows >= KH: nothing to do, the column pass takes them as zeros (inv_col_k)
     }
 }
 template <int W, int H, bool QM, bool DIST = false, class C = CfgRuntime>
@@ -838,7 +836,11 @@ SVT_HD void inv_col_k(const DevBlock& d, int c, const int* buf, PIX* pix, int pm
     const Clamp k16(16);  // the column stage range: 16 bits for bd 8 / 10
     int x[H];
 #pragma unroll
-    for (int r = 0; r < H; ++r) x[r] = src[r * G::LD];  // already clamped to 16 bits by the row pass
+    // already clamped to 16 bits by the row pass.  Rows >= KH (64-row sizes) hold the inverse row
+    // transform of all-zero coefficient rows, i.e. zeros (EbTransforms.c:8299): they are neither
+    // written by the row pass nor read here, and as compile-time zeros they fold the first stages
+    // of the 64-point network away.
+    for (int r = 0; r < H; ++r) x[r] = r < G::KH ? src[r * G::LD] : 0;
     if constexpr (FAST) inv1d_k<H, KIND>(x, NoClamp());  // inside fast_limit: no clamp can bind
     else inv1d_k<H, KIND>(x, k16);
     // check_range (EbTransforms.c:7794) clamps the residual to +-(2^(7+bd) - 1 + (914 << (bd-7))),

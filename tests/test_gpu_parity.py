@@ -332,23 +332,16 @@ def test_full_size_properties(cfg):
     again = run_gpu(batch, qm=qm)
     for k in KEYS:
         assert np.array_equal(out[k], again[k]), k
-    # (2) a random sample of blocks equals the oracle
-    rng = np.random.default_rng(1)
-    idx = np.sort(rng.choice(batch.n_blocks, 6000, replace=False))
-    sub = _subset(batch, idx)
-    ora = run_oracle(sub, tables(batch.bd), load_scans(), qm=qm, threads=8)
-    assert np.array_equal(out["eob"][idx], ora["eob"])
-    assert np.array_equal(out["energy"][idx], ora["energy"])
-    for j, i in enumerate(idx):
-        s = int(batch.blocks["tx_size"][i])
-        n = max_eob(s)
-        a, b = int(batch.blocks["coeff_off"][i]), int(sub.blocks["coeff_off"][j])
-        assert np.array_equal(out["qcoeff"][a:a + n], ora["qcoeff"][b:b + n]), i
-        assert np.array_equal(out["dqcoeff"][a:a + n], ora["dqcoeff"][b:b + n]), i
-        w, h = wl.TX_W[s], wl.TX_H[s]
-        o, st = int(batch.blocks["rec_off"][i]), int(batch.blocks["rec_stride"][i])
-        rows = (o + st * np.arange(h))[:, None] + np.arange(w)[None, :]
-        assert np.array_equal(out["recon"][rows], ora["recon"][rows]), i
+    # (2) EVERY block equals the checker: the compiled reference over the whole batch (its AVX2 RTCD
+    # path, plus highbd_quantize_b_helper_c for the qmatrix blocks) where oracle/_ref exists on the
+    # box, else the oracle restatement
+    from oracle_lib import ref, run_ref
+    if ref() is not None:
+        ora = run_ref(batch, tables(batch.bd), threads=16, qm=qm)
+    else:
+        ora = run_oracle(batch, tables(batch.bd), load_scans(), qm=qm, threads=16)
+    for k in KEYS:
+        assert np.array_equal(out[k], ora[k]), (cfg, k, np.nonzero(out[k] != ora[k])[0][:5])
     # (3) the three RTCD-level stages chained == fused
     q = run_gpu(batch, stages=2, qm=qm, coeff_in=out["coeff"])
     assert np.array_equal(q["qcoeff"], out["qcoeff"]) and np.array_equal(q["eob"], out["eob"])

@@ -1,11 +1,18 @@
 #!/bin/bash
-# tools/ab.sh OUTPREFIX VARIANT...   A/B the library builds under tools/variants on the GPU box
-out=$1; shift
+# tools/ab.sh TAG VARIANT... : on the GPU box, for each variant library tools/variants/libsvtgpu_V.so
+# ("base" = the in-tree library): headline bench with parity gate and per-kernel table.
+tag=$1; shift
 for v in "$@"; do
-  export SVTGPU_LIB=$PWD/tools/variants/libsvtgpu_$v.so
-  python -m pytest tests/test_gpu_parity.py -x -q 2>&1 | tail -2 > gpurun_out/${out}_${v}_pytest.log
-  python bench.py --steps 20 --warmup 5 --per-kernel --no-cpu > gpurun_out/${out}_${v}.json 2> gpurun_out/${out}_${v}.err
-  python bench.py --steps 20 --warmup 5 --kernel-only >> gpurun_out/${out}_${v}.json 2>> gpurun_out/${out}_${v}.err
-  python bench.py --steps 10 --warmup 5 --per-kernel --no-cpu --workload 4k10qm > gpurun_out/${out}_${v}_4k.json 2> gpurun_out/${out}_${v}_4k.err
+  lib=""; [ "$v" != base ] && lib=$PWD/tools/variants/libsvtgpu_$v.so
+  SVTGPU_LIB=$lib python bench.py --no-extra --no-cpu --per-kernel > gpurun_out/${tag}_${v}.json 2> gpurun_out/${tag}_${v}.err
+  echo "== $v rc=$?"
+  grep -h per-kernel gpurun_out/${tag}_${v}.err | cut -c1-700
+  python - <<PY
+import json
+try:
+    d = json.load(open("gpurun_out/${tag}_${v}.json")); r = d.get("roofline") or {}
+    print("$v", "value", d.get("value"), "ms", d.get("ms_per_step"), "frac", r.get("frac"), "step", r.get("step_frac"), "e2e", (d.get("e2e") or {}).get("value"), "parity", (d.get("parity") or {}).get("ok"))
+except Exception as e:
+    print("$v: no line", e)
+PY
 done
-tail -n 3 gpurun_out/${out}_*_pytest.log
