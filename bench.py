@@ -414,11 +414,92 @@ def sweep(pkg, g8, local_rank, dev, st):
     return out
 
 
+def copy_ceiling(torch, dev, batch, hb, steps, barrier, world, total_samples):
+    """What the PCIe link and the host memory allow for the headline e2e call: per picture the same
+    H2D (residual, prediction) and D2H (qcoeff, dqcoeff, eob, energy, recon) byte counts, from / to
+    the same page-locked buffers, on one upload and one download stream, no kernels."""
+    import torch.distributed as dist
+    up, down = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    frames = batch.frames()
+    pairs = []
+    for k, fr in enumerate(frames):
+        res, pred, _ = hb.frame_in(k)
+        out = hb.frame_out(k)
+        h_in = [torch.from_numpy(res.view(np.uint8)), torch.from_numpy(pred.view(np.uint8))]
+        h_out = [torch.from_numpy(v.view(np.uint8).reshape(-1)) for v in out.values() if v is not None]
+        pairs.append((h_in, h_out))
+    n_in, n_out = len(pairs[0][0]), len(pairs[0][1])
+    max_in = [max(hi[j].numel() for hi, _ in pairs) for j in range(n_in)]
+    max_out = [max(ho[j].numel() for _, ho in pairs) for j in range(n_out)]
+    d_in = [[torch.empty(n, dtype=torch.uint8, device=dev) for n in max_in] for _ in range(3)]
+    d_out = [[torch.empty(n, dtype=torch.uint8, device=dev) for n in max_out] for _ in range(3)]
+
+    def one():
+        for k, (hi, ho) in enumerate(pairs):
+            lane = k % 3
+            with torch.cuda.stream(up):
+                for dt, ht in zip(d_in[lane], hi):
+                    dt[:ht.numel()].copy_(ht, non_blocking=True)
+            with torch.cuda.stream(down):
+                for dt, ht in zip(d_out[lane], ho):
+                    ht.copy_(dt[:ht.numel()], non_blocking=True)
+        up.synchronize()
+        down.synchronize()
+    ok = all(t.is_pinned() for hi, ho in pairs for t in hi + ho)
+    for _ in range(2):
+        one()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        one()
+    barrier()
+    wall = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(wall, op=dist.ReduceOp.MAX)
+    sec = float(wall.item()) / steps
+    h2d = sum(t.numel() for hi, _ in pairs for t in hi)
+    d2h = sum(t.numel() for _, ho in pairs for t in ho)
+    return {"value": total_samples / sec / 1e6, "unit": UNIT, "ms_per_step": sec * 1e3,
+            "d2h_GBps_per_gpu": d2h / sec / 1e9, "h2d_GBps_per_gpu": h2d / sec / 1e9, "pinned": ok,
+            "what": "copies only, same bytes and buffers as e2e, one upload + one download stream per GPU"}
+
+
+def place_near_gpu(local_rank):
+    """Run this rank on the CPUs of its GPU's NUMA node (sysfs local_cpulist of the PCI device), so
+    that the page-locked buffers it allocates afterwards are node-local (first touch) and its
+    copies do not cross the socket interconnect.  Host plumbing only; returns what it did."""
+    info = {"numa_node": None, "cpus": None, "bound": False}
+    try:
+        bus = subprocess.run(["nvidia-smi", "--query-gpu=pci.bus_id", "--format=csv,noheader", "-i", str(local_rank)],
+                             capture_output=True, text=True, timeout=20).stdout.strip().lower()
+        if bus.count(":") == 2 and len(bus.split(":")[0]) == 8:
+            bus = bus[4:]  # 00000000:1b:00.0 -> 0000:1b:00.0
+        base = f"/sys/bus/pci/devices/{bus}"
+        info["pci"] = bus
+        info["numa_node"] = int(open(base + "/numa_node").read())
+        cpulist = open(base + "/local_cpulist").read().strip()
+        cpus = set()
+        for part in cpulist.split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        allowed = os.sched_getaffinity(0)
+        use = cpus & allowed
+        info["cpus"] = cpulist
+        if use and use != allowed:
+            os.sched_setaffinity(0, use)
+            info["bound"] = True
+        info["allowed_cpus"] = len(allowed)
+    except Exception as e:  # placement is an optimisation, never a requirement
+        info["error"] = str(e)[:120]
+    return info
+
+
 def gpu_arm(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
     import cidana_svt_av1_b200 as pkg
 
+    placement = place_near_gpu(local_rank)
     dev = torch.device("cuda", local_rank)
     torch.cuda.set_device(dev)
     if world > 1:
@@ -510,39 +591,80 @@ def gpu_arm(args, rank, world, local_rank):
             pass
 
     # ---- e2e: host buffers in, host buffers out, through the public host-pipeline call -----------
-    # Every step: descriptor sort + upload, H2D of residual and prediction from page-locked memory,
-    # the kernels, D2H of qcoeff, dqcoeff, eob, energy and recon into page-locked memory; pictures
-    # of the batch are pipelined over the library's lanes (svtgpu_submit_host / svtgpu_wait_host).
-    hb = g.host_buffers(batch, pinned=True)
-    h2d = batch.residual.nbytes + batch.pred.nbytes + batch.n_blocks * 32
-    d2h = sum(v.nbytes for v in hb.out.values() if v is not None)
-
-    def e2e_step():
-        g.run_host(batch, bufs=hb)
-
-    e2e_steps = max(2, min(args.steps, 10))
-    for _ in range(3):  # three passes: every picture of the batch has met every lane of the pipeline
-        e2e_step()
-    barrier()
-    t0 = time.perf_counter()
-    e2e_each = []
+    # Every step: H2D of residual and prediction from page-locked memory, the kernels, D2H of the
+    # outputs into page-locked memory; pictures of the batch are pipelined over the library's lanes
+    # (svtgpu_submit_host / svtgpu_wait_host).  The geometry repeats from step to step, so the
+    # per-picture plans are made once (svtgpu_plan_create) and passed with every submission.
     L = pkg.api.lib()
     L.svtgpu_debug_host_allocs.restype = ctypes.c_longlong
-    for _ in range(e2e_steps):
-        t1 = time.perf_counter()
-        e2e_step()
-        e2e_each.append((round((time.perf_counter() - t1) * 1e3, 2), int(L.svtgpu_debug_host_allocs())))
-    barrier()
-    e2e_wall = time.perf_counter() - t0
+    e2e_steps = max(2, min(args.steps, 10))
+    plans = g.frame_plans(batch)
+
+    def e2e_measure(work, hb, stages, plans_):
+        def one():
+            g.run_host(work, stages=stages, bufs=hb, plans=plans_)
+        for _ in range(3):  # three passes: every picture of the batch has met every lane of the pipeline
+            one()
+        barrier()
+        t0, each = time.perf_counter(), []
+        for _ in range(e2e_steps):
+            t1 = time.perf_counter()
+            one()
+            each.append((round((time.perf_counter() - t1) * 1e3, 2), int(L.svtgpu_debug_host_allocs())))
+        barrier()
+        wall = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(wall, op=dist.ReduceOp.MAX)
+        return total_samples * e2e_steps / float(wall.item()) / 1e6, each
+
+    def nbytes(*arrays):
+        return int(sum(a.nbytes for a in arrays if a is not None))
+
+    # (1) the headline: every output of the path (qcoeff, dqcoeff, eob, energy, recon)
+    hb = g.host_buffers(batch, pinned=True)
+    h2d = nbytes(batch.residual, batch.pred)
+    d2h = nbytes(*hb.out.values())
+    e2e_val, e2e_each = e2e_measure(batch, hb, pkg.api.STAGE_ALL, plans)
     if rank == 0:
         print("e2e ms per step:", e2e_each, file=sys.stderr, flush=True)
-    e2e_s = torch.tensor([e2e_wall], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-    e2e_val = total_samples * e2e_steps / float(e2e_s.item()) / 1e6
     # the host arrays the e2e call filled go through the same gate
     e2e_par = job.parity({k: hb.out[k] for k in PARITY_KEYS})
     e2e_ok = all_ok(e2e_par["ok"], world, dev)
+    want = job.runner().outputs()  # the reference pass the gate just made
+
+    # (2) what the encode pass consumes (EbCodingLoop.c:697-731 feeds recon_coeff only to the inverse
+    # transform, which has already run here): qcoeff + eob + recon come back, dqcoeff stays on the GPU
+    hb2 = g.host_buffers(batch, pinned=True)
+    hb2.out["dqcoeff"] = None
+    enc_val, _ = e2e_measure(batch, hb2, pkg.api.STAGE_ALL, plans)
+    enc_ok = all_ok(all(np.array_equal(hb2.out[k], want[k]) for k in ("qcoeff", "eob", "energy", "recon")), world, dev)
+    enc = {"value": enc_val if enc_ok else None, "unit": UNIT, "what": "qcoeff + eob + energy + recon out (no dqcoeff)",
+           "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": nbytes(*hb2.out.values()), "parity_ok": enc_ok}
+
+    # (3) what mode decision consumes: source + prediction in; eob, distortion pair and
+    # reconstruction out, no coefficient arrays
+    md = None
+    if qm is None:
+        src_batch = batch.with_source()
+        hb3 = g.host_buffers(src_batch, pinned=True, dist=True, coeffs=False)
+        md_stages = pkg.api.STAGE_ALL | pkg.api.STAGE_RESIDUAL
+        md_val, _ = e2e_measure(src_batch, hb3, md_stages, plans)
+        # residual = src - pred is what the reference pass transforms; its distortion pair is pinned
+        # by the tests (tests/test_gpu_parity.py: run_oracle_md), here eob and recon are compared
+        r3 = make_cpu_runner(src_batch, tables, qm)
+        r3.run(os.cpu_count() or 1)
+        w3 = r3.outputs()
+        md_ok = all_ok(all(np.array_equal(hb3.out[k], w3[k]) for k in ("eob", "recon")), world, dev)
+        md = {"value": md_val if md_ok else None, "unit": UNIT,
+              "what": "source + prediction in; eob + distortion pair + energy + recon out (no coefficient arrays)",
+              "h2d_bytes_per_step": nbytes(src_batch.src, src_batch.pred), "d2h_bytes_per_step": nbytes(*hb3.out.values()),
+              "parity_ok": md_ok}
+        del hb3, r3
+
+    # (4) the ceiling of (1): the same bytes through the same page-locked buffers, copies only
+    ceiling = copy_ceiling(torch, dev, batch, hb, e2e_steps, barrier, world, total_samples)
+    for pl_ in plans:
+        pl_.close()
 
     extra = {}
     if not args.no_extra:
@@ -566,7 +688,8 @@ def gpu_arm(args, rank, world, local_rank):
                 "gpu_launches": launches,
                 "e2e": {"value": e2e_val if e2e_ok else None, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                         "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
-                        "parity": dict(e2e_par, ok=e2e_ok, ranks=world)},
+                        "parity": dict(e2e_par, ok=e2e_ok, ranks=world), "copy_only_ceiling": ceiling},
+                "e2e_encode_pass": enc, "e2e_md": md, "placement": placement,
                 "extra": extra}
         emit(line)
     if world > 1:
