@@ -53,6 +53,13 @@ struct Tls {
     int32_t* d_coeff = nullptr;  // 3 x kMaxPix
     int16_t* d_tab = nullptr;
     uint64_t* d_small = nullptr;
+    // tx-type search of one block (svtgpu_tx_search_block): up to 16 candidates in one launch
+    SvtGpuPlan plan16;
+    DevBlock* h_blk16 = nullptr;       // pinned, 16 descriptors
+    int32_t* d_q16 = nullptr;          // 16 x 1024 quantised coefficients
+    int32_t* h_q16 = nullptr;          // pinned
+    uint64_t* d_out16 = nullptr;       // [0..15] energy, [16..47] distortion pairs, then 16 x u16 eob
+    uint64_t* h_out16 = nullptr;       // pinned
 
     void init() {
         if (ctx) return;
@@ -72,6 +79,13 @@ struct Tls {
         CKA(cudaMalloc(&plan.d_blocks, sizeof(DevBlock)));
         plan.ctx = ctx;
         plan.n = 1;
+        CKA(cudaMalloc(&plan16.d_blocks, 16 * sizeof(DevBlock)));
+        plan16.ctx = ctx;
+        CKA(cudaMallocHost(&h_blk16, 16 * sizeof(DevBlock)));
+        CKA(cudaMalloc(&d_q16, 16 * 1024 * sizeof(int32_t)));
+        CKA(cudaMallocHost(&h_q16, 16 * 1024 * sizeof(int32_t)));
+        CKA(cudaMalloc(&d_out16, 52 * sizeof(uint64_t)));
+        CKA(cudaMallocHost(&h_out16, 52 * sizeof(uint64_t)));
         // the quantizer table of this context is the single row staged in d_tab
         ctx->d_qtables = d_tab;
         ctx->n_qrows = 1;
@@ -80,6 +94,8 @@ struct Tls {
         if (!ctx) return;
         ctx->d_qtables = nullptr;  // owned here, not by the context
         cudaStreamSynchronize(ctx->stream);
+        cudaFree(plan16.d_blocks); cudaFree(d_q16); cudaFree(d_out16);
+        cudaFreeHost(h_blk16); cudaFreeHost(h_q16); cudaFreeHost(h_out16);
         cudaFree(plan.d_blocks); cudaFree(d_res); cudaFree(d_pix); cudaFree(d_coeff);
         cudaFree(d_tab); cudaFree(d_small);
         cudaFreeHost(h_res); cudaFreeHost(h_pix); cudaFreeHost(h_coeff); cudaFreeHost(h_tab);
@@ -344,6 +360,63 @@ extern "C" int svtgpu_av1_inv_transform_recon(int32_t* coeff_buffer, uint8_t* re
     inv_host(txsize, coeff_buffer, px, int32_t(recon_stride), transform_type,
              bit_increment ? 10 : 8, true);
     return 0;
+}
+
+// ---- tx-type search of one block ------------------------------------------------------------------
+// The per-type loop of encode_pass_tx_search / ProductFullLoopTxSearch (EbFullLoop.c:1127-1318,
+// :927-1100) runs av1_estimate_transform -> av1_quantize_inv_quantize ->
+// picture_full_distortion32_bits once per candidate type.  Here the residual is staged once and
+// all candidate types of the block go through ONE launch of the fused path (forward + quantise +
+// distortion pair): the caller keeps its own rate estimate and cost, candidate by candidate.
+extern "C" int svtgpu_tx_search_block(const int16_t* residual, uint32_t residual_stride, uint8_t tx_size,
+                                      const uint8_t* tx_types, int n_types, const int16_t* zbin,
+                                      const int16_t* round, const int16_t* quant, const int16_t* quant_shift,
+                                      const int16_t* dequant, uint32_t bit_increment, int32_t* quant_coeff,
+                                      uint16_t* eob, uint64_t* dist, uint64_t* three_quad_energy) {
+    if (!residual || !tx_types || n_types < 1 || n_types > 16 || tx_size > 18 || !quant_coeff || !eob || !dist)
+        return SVTGPU_ERR_ARG;
+    for (int k = 0; k < n_types; ++k) check_pair(tx_size, tx_types[k]);
+    Tls& t = g_tls;
+    t.init();
+    const int s = tx_size, w = kTxW[s], h = kTxH[s], n = max_eob(s), bd = bit_increment ? 10 : 8;
+    for (int r = 0; r < h; ++r) memcpy(t.h_res + r * w, residual + size_t(r) * residual_stride, w * sizeof(int16_t));
+    const int16_t* rows[5] = { zbin, round, quant, quant_shift, dequant };
+    for (int i = 0; i < 5; ++i) memcpy(t.h_tab + 8 * i, rows[i], 2 * sizeof(int16_t));
+    for (int k = 0; k < n_types; ++k) {
+        DevBlock& d = t.h_blk16[k];
+        d.res_off = 0; d.res_stride = w; d.rec_off = 0; d.rec_stride = w;
+        d.coeff_off = uint32_t(k * n); d.qrow = 0; d.id = uint32_t(k);
+        d.meta = make_meta(tx_types[k], bd, 0, false, false);
+    }
+    cudaStream_t st = t.ctx->stream;
+    CKA(cudaMemcpyAsync(t.d_res, t.h_res, w * h * sizeof(int16_t), cudaMemcpyHostToDevice, st));
+    CKA(cudaMemcpyAsync(t.d_tab, t.h_tab, 40 * sizeof(int16_t), cudaMemcpyHostToDevice, st));
+    CKA(cudaMemcpyAsync(t.plan16.d_blocks, t.h_blk16, n_types * sizeof(DevBlock), cudaMemcpyHostToDevice, st));
+    for (int i = 0; i < 19; ++i) { t.plan16.first[i] = 0; t.plan16.count[i] = 0; }
+    t.plan16.count[s] = n_types;
+    t.plan16.n = n_types;
+    t.plan16.max_qrow = 0;
+    t.plan16.bd_uniform = bd;
+    SvtGpuBuffers b;
+    memset(&b, 0, sizeof(b));
+    b.residual = t.d_res;
+    b.qcoeff = t.d_q16;
+    b.energy = t.d_out16;
+    b.dist = t.d_out16 + 16;
+    b.eob = reinterpret_cast<uint16_t*>(t.d_out16 + 48);
+    if (svtgpu_run_internal(t.ctx, &t.plan16, &b, STAGE_FWD | STAGE_QUANT, st) != SVTGPU_OK) die("svtgpu_run (tx search)");
+    CKA(cudaMemcpyAsync(t.h_q16, t.d_q16, size_t(n_types) * n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    CKA(cudaMemcpyAsync(t.h_out16, t.d_out16, 52 * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+    CKA(cudaStreamSynchronize(st));
+    memcpy(quant_coeff, t.h_q16, size_t(n_types) * n * sizeof(int32_t));
+    const uint16_t* e16 = reinterpret_cast<const uint16_t*>(t.h_out16 + 48);
+    for (int k = 0; k < n_types; ++k) {
+        eob[k] = e16[k];
+        dist[2 * k] = t.h_out16[16 + 2 * k];
+        dist[2 * k + 1] = t.h_out16[16 + 2 * k + 1];
+        if (three_quad_energy) three_quad_energy[k] = t.h_out16[k];
+    }
+    return SVTGPU_OK;
 }
 
 // ---- the slot table an installer walks ------------------------------------------

@@ -265,6 +265,20 @@ int svtgpu_av1_inv_transform_recon8bit(int32_t *coeff_buffer, uint8_t *recon_buf
                                        uint32_t recon_stride, uint8_t txsize,
                                        uint8_t transform_type, int component_type, uint32_t eob);
 
+/* The per-type loop of encode_pass_tx_search (EbFullLoop.c:1127-1318) and ProductFullLoopTxSearch
+ * (:927-1100) for ONE transform block: the residual is staged once and every candidate type in
+ * tx_types[0 .. n_types) (<= 16, each legal for tx_size) goes through one launch of forward
+ * transform + quantiser + transform-domain distortion.  Outputs per candidate k:
+ * quant_coeff[k * max_eob .. ), eob[k], dist[2k] / dist[2k+1] = tuFullDistortion
+ * {DIST_CALC_RESIDUAL, DIST_CALC_PREDICTION} after the energy term and the tx-scale shift
+ * (:1231-1257), three_quad_energy[k] (optional).  The caller keeps the rate estimate and the cost
+ * (Av1TuEstimateCoeffBits, av1_tu_calc_cost_luma) and applies them candidate by candidate. */
+int svtgpu_tx_search_block(const int16_t *residual, uint32_t residual_stride, uint8_t tx_size,
+                           const uint8_t *tx_types, int n_types, const int16_t *zbin,
+                           const int16_t *round, const int16_t *quant, const int16_t *quant_shift,
+                           const int16_t *dequant, uint32_t bit_increment, int32_t *quant_coeff,
+                           uint16_t *eob, uint64_t *dist, uint64_t *three_quad_energy);
+
 /* ------------------------------------------------------------------------------------------ */
 /* Level A: RTCD slots (aom_dsp_rtcd.h)                                                        */
 /* ------------------------------------------------------------------------------------------ */

@@ -34,12 +34,15 @@
 #include "EbPictureControlSet.h"
 #include "EbTransforms.h"
 #include "EbSvtAv1Enc.h"
+#include "EbEncDecProcess.h"
+#include "EbEntropyCoding.h"
+#include "EbRateDistortionCost.h"
 #endif
 #include "svt_gpu.h"
 
 static void *g_lib;
-static int g_level_a, g_level_b;
-static long long g_calls[4]; /* estimate_transform, quantize_inv_quantize, recon, recon8bit */
+static int g_level_a, g_level_b, g_level_s;
+static long long g_calls[6]; /* estimate_transform, quantize_inv_quantize, recon, recon8bit, tx searches, candidates */
 
 static void die(const char *what, const char *arg) {
     fprintf(stderr, "[svtgpu-preload] %s %s\n", what, arg ? arg : "");
@@ -58,21 +61,24 @@ static void (*p_quant)(const int16_t *, const int16_t *, const int16_t *, const 
                        uint32_t *, uint32_t, uint8_t, int);
 static int (*p_recon)(int32_t *, uint8_t *, uint32_t, uint8_t, uint32_t, uint8_t, int, uint32_t);
 static int (*p_recon8)(int32_t *, uint8_t *, uint32_t, uint8_t, uint8_t, int, uint32_t);
+static int (*p_txsearch)(const int16_t *, uint32_t, uint8_t, const uint8_t *, int, const int16_t *, const int16_t *,
+                         const int16_t *, const int16_t *, const int16_t *, uint32_t, int32_t *, uint16_t *,
+                         uint64_t *, uint64_t *);
 
 static long long (*p_launches)(void);
 static void report(void) {
     if (!g_lib) return;
     fprintf(stderr, "[svtgpu-preload] kernels launched by libsvtgpu.so: %lld; level-B calls served: "
             "estimate_transform %lld, quantize_inv_quantize %lld, inv_transform_recon %lld, "
-            "inv_transform_recon8bit %lld\n", p_launches ? p_launches() : -1,
-            g_calls[0], g_calls[1], g_calls[2], g_calls[3]);
+            "inv_transform_recon8bit %lld; batched tx-type searches %lld (%lld candidates)\n",
+            p_launches ? p_launches() : -1, g_calls[0], g_calls[1], g_calls[2], g_calls[3], g_calls[4], g_calls[5]);
 }
 
 static void install(void) {
     const char *path = getenv("SVT_GPU_LIB");
     const char *lvl = getenv("SVT_GPU_LEVEL");
 #ifdef SVT_GPU_LEVEL_B
-    if (!lvl) lvl = "AB";
+    if (!lvl) lvl = "ABS";
 #else
     if (!lvl) lvl = "A";
 #endif
@@ -97,12 +103,17 @@ static void install(void) {
         p_recon = need("svtgpu_av1_inv_transform_recon");
         p_recon8 = need("svtgpu_av1_inv_transform_recon8bit");
         g_level_b = 1;
+        if (strchr(lvl, 'S')) {
+            p_txsearch = need("svtgpu_tx_search_block");
+            g_level_s = 1;
+        }
 #else
         die("built without -DSVT_GPU_LEVEL_B; SVT_GPU_LEVEL =", lvl);
 #endif
     }
-    fprintf(stderr, "[svtgpu-preload] %d RTCD slots rebound to libsvtgpu.so, level-B entry points %s\n",
-            g_level_a, g_level_b ? "interposed" : "left to the encoder");
+    fprintf(stderr, "[svtgpu-preload] %d RTCD slots rebound to libsvtgpu.so, level-B entry points %s, tx-type search %s\n",
+            g_level_a, g_level_b ? "interposed" : "left to the encoder",
+            g_level_s ? "batched (one launch per block)" : "left to the encoder");
 }
 
 /* EbSvtAv1Enc.h:439 -- EbErrorType eb_init_encoder(EbComponentType *svt_enc_component) */
@@ -229,5 +240,109 @@ EbErrorType av1_inv_transform_recon8bit(int32_t *coeff_buffer, uint8_t *recon_bu
     __atomic_fetch_add(&g_calls[3], 1, __ATOMIC_RELAXED);
     return (EbErrorType)p_recon8(coeff_buffer, recon_buffer, recon_stride, txsize, transform_type,
                                  component_type, eob);
+}
+/* SURVEY 8f-2 wired in: encode_pass_tx_search (EbFullLoop.c:1127-1318), the tx-type search the
+ * encode pass runs per luma transform block at enc-mode >= 6 (TX_SEARCH_ENC_DEC,
+ * EbPictureDecisionProcess.c:944-960).  The reference walks the candidate types one after another
+ * around av1_estimate_transform -> av1_quantize_inv_quantize -> picture_full_distortion32_bits and
+ * prices each with Av1TuEstimateCoeffBits + av1_tu_calc_cost_luma.  Here the candidate list is
+ * built with the reference's own skip rules, ALL candidates go through one
+ * svtgpu_tx_search_block launch, and the reference's rate estimate and cost are then applied to
+ * them in the same order -- same winner, 1 launch instead of 2 per candidate.  Everything the loop
+ * leaves behind for later code is reproduced: txb_ptr->transform_type, the candidate buffer
+ * fields, eob[0] and the quantised coefficients of the last candidate tried (Av1EncodeLoop
+ * re-transforms the block with the winning type right after, EbCodingLoop.c:655-731).
+ * The 16-bit twin encode_pass_tx_search_hbd is left to the encoder. */
+extern uint8_t allowed_tx_set_a[TX_SIZES_ALL][TX_TYPES];
+void encode_pass_tx_search(PictureControlSet_t *picture_control_set_ptr, EncDecContext_t *context_ptr,
+                           LargestCodingUnit_t *sb_ptr, uint32_t cbQp, EbPictureBufferDesc_t *coeffSamplesTB,
+                           EbPictureBufferDesc_t *residual16bit, EbPictureBufferDesc_t *transform16bit,
+                           EbPictureBufferDesc_t *inverse_quant_buffer, int16_t *transformScratchBuffer,
+                           EbAsm asm_type, uint32_t *count_non_zero_coeffs, uint32_t component_mask,
+                           uint32_t use_delta_qp, uint32_t dZoffset, uint16_t *eob,
+                           MacroblockPlane *candidate_plane) {
+    if (!g_level_s) {
+        static void (*real)(PictureControlSet_t *, EncDecContext_t *, LargestCodingUnit_t *, uint32_t,
+                            EbPictureBufferDesc_t *, EbPictureBufferDesc_t *, EbPictureBufferDesc_t *,
+                            EbPictureBufferDesc_t *, int16_t *, EbAsm, uint32_t *, uint32_t, uint32_t, uint32_t,
+                            uint16_t *, MacroblockPlane *);
+        if (!real) real = dlsym(RTLD_NEXT, "encode_pass_tx_search");
+        real(picture_control_set_ptr, context_ptr, sb_ptr, cbQp, coeffSamplesTB, residual16bit, transform16bit,
+             inverse_quant_buffer, transformScratchBuffer, asm_type, count_non_zero_coeffs, component_mask,
+             use_delta_qp, dZoffset, eob, candidate_plane);
+        return;
+    }
+    CodingUnit_t *cu_ptr = context_ptr->cu_ptr;
+    TransformUnit *txb_ptr = &cu_ptr->transform_unit_array[context_ptr->txb_itr];
+    const uint32_t scratchLumaOffset = context_ptr->blk_geom->tx_org_x[context_ptr->txb_itr] +
+                                       context_ptr->blk_geom->tx_org_y[context_ptr->txb_itr] * SB_STRIDE_Y;
+    const uint32_t coeff1dOffset = context_ptr->coded_area_sb;
+    const int32_t is_inter = context_ptr->is_inter;
+    const TxSize txSize = context_ptr->blk_geom->txsize[context_ptr->txb_itr];
+    const PictureParentControlSet_t *ppcs = picture_control_set_ptr->parent_pcs_ptr;
+    const TxSetType tx_set_type = get_ext_tx_set_type(txSize, is_inter, ppcs->reduced_tx_set_used);
+
+    /* the candidate list, by the loop's own rules (EbFullLoop.c:1174-1186) */
+    uint8_t types[TX_TYPES];
+    int n_types = 0;
+    for (int32_t t = DCT_DCT; t < TX_TYPES; ++t) {
+        if (ppcs->tx_search_reduced_set)
+            if (!allowed_tx_set_a[txSize][t]) continue;
+        const int32_t eset = get_ext_tx_set(txSize, is_inter, ppcs->reduced_tx_set_used);
+        if (eset <= 0) continue;
+        if (av1_ext_tx_used[tx_set_type][t] == 0) continue;
+        types[n_types++] = (uint8_t)t;
+    }
+    TxType best_tx_type = DCT_DCT;
+    if (n_types > 0) {
+        /* BIT_INCREMENT_8BIT, COMPONENT_LUMA: the *Md tables (EbFullLoop.c:548-557) */
+        const uint32_t q = ppcs->base_qindex;
+        static __thread int32_t qc[TX_TYPES * 1024];
+        uint16_t eobs[TX_TYPES];
+        uint64_t dist[TX_TYPES][2], energy[TX_TYPES];
+        const int n = av1_get_max_eob(txSize);
+        if (p_txsearch(((int16_t *)residual16bit->buffer_y) + scratchLumaOffset, residual16bit->stride_y, (uint8_t)txSize,
+                       types, n_types, ppcs->quantsMd.y_zbin[q], ppcs->quantsMd.y_round[q], ppcs->quantsMd.y_quant[q],
+                       ppcs->quantsMd.y_quant_shift[q], ppcs->deqMd.y_dequant_QTX[q], 0, qc, eobs, &dist[0][0],
+                       energy) != 0)
+            die("svtgpu_tx_search_block failed", NULL);
+        __atomic_fetch_add(&g_calls[4], 1, __ATOMIC_RELAXED);
+        __atomic_fetch_add(&g_calls[5], n_types, __ATOMIC_RELAXED);
+        uint64_t bestFullCost = UINT64_MAX, y_full_cost, y_tu_coeff_bits;
+        int32_t *qdst = ((int32_t *)coeffSamplesTB->buffer_y) + coeff1dOffset;
+        for (int k = 0; k < n_types; ++k) {
+            const TxType tx_type = (TxType)types[k];
+            context_ptr->three_quad_energy = energy[k];
+            y_tu_coeff_bits = 0;
+            memcpy(qdst, qc + (size_t)k * n, (size_t)n * sizeof(int32_t)); /* what the quantiser would have left */
+            eob[0] = eobs[k];
+            const uint32_t yCountNonZeroCoeffsTemp = eobs[k];
+            if (yCountNonZeroCoeffsTemp == 0 && tx_type != DCT_DCT) continue;
+            txb_ptr->transform_type[PLANE_TYPE_Y] = tx_type;
+            ModeDecisionCandidateBuffer_t *candidateBuffer = context_ptr->md_context->candidate_buffer_ptr_array[0];
+            candidateBuffer->candidate_ptr->transform_type[PLANE_TYPE_Y] = cu_ptr->transform_unit_array[context_ptr->txb_itr].transform_type[PLANE_TYPE_Y];
+            candidateBuffer->candidate_ptr->transform_type[PLANE_TYPE_UV] = cu_ptr->transform_unit_array[context_ptr->txb_itr].transform_type[PLANE_TYPE_UV];
+            candidateBuffer->candidate_ptr->type = cu_ptr->prediction_mode_flag;
+            candidateBuffer->candidate_ptr->pred_mode = cu_ptr->pred_mode;
+            Av1TuEstimateCoeffBits(picture_control_set_ptr, candidateBuffer, context_ptr->cu_ptr, coeff1dOffset, 0,
+                                   picture_control_set_ptr->coeff_est_entropy_coder_ptr, coeffSamplesTB,
+                                   yCountNonZeroCoeffsTemp, 0, 0, &y_tu_coeff_bits, &y_tu_coeff_bits, &y_tu_coeff_bits,
+                                   context_ptr->blk_geom->txsize[context_ptr->txb_itr],
+                                   context_ptr->blk_geom->txsize_uv[context_ptr->txb_itr], COMPONENT_LUMA, asm_type);
+            av1_tu_calc_cost_luma(context_ptr->cu_ptr->luma_txb_skip_context, candidateBuffer->candidate_ptr,
+                                  context_ptr->txb_itr, context_ptr->blk_geom->txsize[context_ptr->txb_itr],
+                                  yCountNonZeroCoeffsTemp, dist[k], &y_tu_coeff_bits, &y_full_cost,
+                                  context_ptr->full_lambda);
+            if (y_full_cost < bestFullCost) {
+                bestFullCost = y_full_cost;
+                best_tx_type = tx_type;
+            }
+        }
+    }
+    txb_ptr->transform_type[PLANE_TYPE_Y] = best_tx_type;
+    /* For Inter blocks, transform type of chroma follows luma transfrom type */
+    if (is_inter) txb_ptr->transform_type[PLANE_TYPE_UV] = txb_ptr->transform_type[PLANE_TYPE_Y];
+    (void)sb_ptr; (void)cbQp; (void)transform16bit; (void)inverse_quant_buffer; (void)transformScratchBuffer;
+    (void)count_non_zero_coeffs; (void)component_mask; (void)use_delta_qp; (void)dZoffset; (void)candidate_plane;
 }
 #endif /* SVT_GPU_LEVEL_B */

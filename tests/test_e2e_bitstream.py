@@ -91,6 +91,9 @@ def test_reference_encoder_is_deterministic_10bit(tmp_path):
 @needs_app
 @pytest.mark.parametrize("level,w,h,n,qp,bd", [("A", 320, 192, 6, 30, 8), ("AB", 320, 192, 6, 30, 8),
                                                ("AB", 640, 384, 4, 45, 8),
+                                               # S: encode_pass_tx_search batched, one launch per block
+                                               ("ABS", 320, 192, 6, 30, 8), ("ABS", 640, 384, 4, 45, 8),
+                                               ("BS", 320, 192, 4, 20, 8),
                                                # 10-bit: Av1EncodeLoop16bit (EbCodingLoop.c:1020) ->
                                                # av1_inv_transform_recon (EbTransforms.c:8905), and mode
                                                # decision quantising chroma with the 8-bit *Md tables
@@ -106,6 +109,11 @@ def test_bitstream_identical_with_gpu_path(tmp_path, level, w, h, n, qp, bd):
     print(f"\n{w}x{h} x{n} q{qp} {bd}-bit level {level}: reference {t_ref:.1f} s, GPU path {t_gpu:.1f} s, "
           f"{os.path.getsize(ref)} bytes\n" + "\n".join(l for l in log.splitlines() if "svtgpu" in l))
     assert open(ref, "rb").read() == open(gpu, "rb").read()
+    if "S" in level:  # the batched search really ran, with more than one candidate per block
+        served = [l for l in log.splitlines() if "batched tx-type searches" in l]
+        n_search = int(served[-1].split("batched tx-type searches ")[1].split(" ")[0])
+        n_cand = int(served[-1].split("(")[-1].split(" ")[0])
+        assert n_search > 0 and n_cand > 2 * n_search, served
     if bd == 10 and "B" in level:  # the 16-bit reconstruction entry point was really driven
         served = [l for l in log.splitlines() if "level-B calls served" in l]
         assert served and int(served[-1].split("inv_transform_recon ")[1].split(",")[0]) > 0, served

@@ -21,7 +21,7 @@ ap.add_argument("--w", type=int, default=1920)
 ap.add_argument("--h", type=int, default=1080)
 ap.add_argument("--frames", type=int, default=10)
 ap.add_argument("--qp", type=int, default=30)
-ap.add_argument("--level", default="AB")
+ap.add_argument("--level", default="ABS")
 ap.add_argument("--bd", type=int, default=8)
 a = ap.parse_args()
 with tempfile.TemporaryDirectory() as d:
