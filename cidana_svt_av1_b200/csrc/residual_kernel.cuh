@@ -662,7 +662,7 @@ SVT_HD void inv_row_store(int (&x)[W], int* row, bool bd10) {
 template <int W, int H, int KIND, bool QM, bool DIST, class C = CfgRuntime>
 SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int* buf, const int16_t* isc,
                   int& eob_max, unsigned long long& energy_sum, unsigned long long (&dsum)[2],
-                  int* fast_flag, RowAux& aux) {
+                  int* fast_flag, RowAux& aux, int* eob_slot = nullptr) {
     static_assert(!(QM && DIST), "the distortion outputs are built for the flat quantizer only");
     using G = Geo<W, H>;
     dsum[0] = dsum[1] = 0;
@@ -785,6 +785,21 @@ SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int
             }
         }
         eob_max = last >= 0 ? int(ld_ro(isc + r * KW + last)) + 1 : 0;
+#if defined(__CUDA_ARCH__)
+        {   // the block's eob = the maximum over its row owners: LB consecutive lanes of one warp, so a
+            // butterfly of shuffles replaces the shared-memory atomicMax (16 lanes on one address were
+            // 7.7 serialised wavefronts per 16x16 block, ncu profiles/r02_v15_*); lane 0 of the group
+            // stores the result, and eob_max goes back as 0 so that the caller has nothing left to do
+            constexpr int LB = H < 32 ? H : 32;
+            const int lane = threadIdx.x & 31, li = r & (LB - 1);
+            const unsigned bmask = LB == 32 ? 0xffffffffu : (((1u << LB) - 1u) << (lane - li));
+            int m = eob_max;
+#pragma unroll
+            for (int k = LB / 2; k > 0; k >>= 1) { const int o = __shfl_xor_sync(bmask, m, k); m = o > m ? o : m; }
+            if (li == 0) *eob_slot = m;
+            eob_max = 0;
+        }
+#endif
         flush_q<W, H, C>(p, d, r, row, x);
     }
 
@@ -819,16 +834,16 @@ SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int
 template <int W, int H, bool QM, bool DIST = false, class C = CfgRuntime>
 SVT_HD void phase_row(const KParams& p, const DevBlock& d, const QRow& q, int r, int* buf,
                       const int16_t* isc, int& e, unsigned long long& en, unsigned long long (&ds)[2],
-                      int* fast_flag, RowAux& aux) {
+                      int* fast_flag, RowAux& aux, int* eob_slot = nullptr) {
     const int kind = hkind(d);
-    if constexpr (W == 64) row_k<W, H, 0, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds, fast_flag, aux);
+    if constexpr (W == 64) row_k<W, H, 0, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds, fast_flag, aux, eob_slot);
     else if constexpr (W == 32) {
-        if (kind == 2) row_k<W, H, 2, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds, fast_flag, aux);
-        else row_k<W, H, 0, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds, fast_flag, aux);
+        if (kind == 2) row_k<W, H, 2, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds, fast_flag, aux, eob_slot);
+        else row_k<W, H, 0, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds, fast_flag, aux, eob_slot);
     } else {
-        if (kind == 0) row_k<W, H, 0, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds, fast_flag, aux);
-        else if (kind == 1) row_k<W, H, 1, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds, fast_flag, aux);
-        else row_k<W, H, 2, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds, fast_flag, aux);
+        if (kind == 0) row_k<W, H, 0, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds, fast_flag, aux, eob_slot);
+        else if (kind == 1) row_k<W, H, 1, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds, fast_flag, aux, eob_slot);
+        else row_k<W, H, 2, QM, DIST, C>(p, d, q, r, buf, isc, e, en, ds, fast_flag, aux, eob_slot);
     }
 }
 // eob rule, three_quad_energy and scaling of the per-TU distortion (EbFullLoop.c:808-835;
@@ -1047,8 +1062,8 @@ residual_kernel(const __grid_constant__ KParams p, int first_block, int count) {
             unsigned long long en, ds[2];
             RowAux aux;
             phase_row<W, H, QM, DIST, C>(p, sh.blk[b], sh.q[b], r, buf + b * G::BLK,
-                                      block_iscan<W, H>(p, sh.blk[b]), e, en, ds, &sh.fast[b], aux);
-            if (e) atomicMax(&sh.eob[b], e);
+                                      block_iscan<W, H>(p, sh.blk[b]), e, en, ds, &sh.fast[b], aux, &sh.eob[b]);
+            if (e) atomicMax(&sh.eob[b], e);  // (device: reduced inside row_k by shuffles, e == 0 here)
             if (G::KW != W || G::KH != H) { if (en) atomicAdd(&sh.energy[b], en); }
             if constexpr (DIST) {
                 if (ds[1]) {
