@@ -202,6 +202,15 @@ SVT_HD constexpr int tx_id(int w, int h) {  // TxSize enum, EbDefinitions.h
 //   stage int16 [NB][H][W]     residual staged by 128-bit coalesced copies (cp.async); after the
 //                              forward column pass the same bytes hold the prediction block and
 //                              then the reconstruction (pixels), copied back out 128 bits at a time
+#ifndef SVT_OCC16  // experiment knobs: resident 256-thread CTA equivalents for the 16- / 32- / 64-point sizes
+#define SVT_OCC16 4
+#endif
+#ifndef SVT_OCC32
+#define SVT_OCC32 4  // v15: 41.6 vs 42.4 us for 32x32 at 64 registers (no spill in the flat kernels); 3 for the qmatrix / distortion variants
+#endif
+#ifndef SVT_OCC64
+#define SVT_OCC64 2
+#endif
 #ifndef SVT_OCC8  // experiment knob: resident 256-thread CTA equivalents for the 4- and 8-point sizes
 #define SVT_OCC8 5  // 6 (42 registers per thread) measured slower: 8x8 51.4 vs 50.5 us, 4x4 23.1 vs 21.2
 #endif
@@ -237,9 +246,12 @@ struct Geo {
     // memory allows, but no more than 5 / 4 / 3 / 2 for 8- / 16- / 32- / 64-point sizes -- measured on B200,
     // CTAs with 64 / 80 / 128 registers per thread beat more, register-starved ones (16x16: 69 vs
     // 74 us at 5 CTAs, 8x8: 58 vs 67 us at 8; 32x32: 56 us at 3 vs 60 us at 2)
-    static constexpr int CTAS_PER_SM =
-        cmin((cmax(W, H) >= 64 ? 2 : (cmax(W, H) >= 32 ? 3 : (cmax(W, H) >= 16 ? 4 : SVT_OCC8))) * 256 / NT,
-             cmax(1, (228 * 1024) / (SMEM_BYTES + 1024 + 108 * NB)));
+    // HEAVY: the qmatrix and distortion variants carry 64-bit arithmetic and spill at the tighter cap
+    static constexpr int ctas_per_sm(bool heavy) {
+        return cmin((cmax(W, H) >= 64 ? SVT_OCC64 : (cmax(W, H) >= 32 ? (heavy ? 3 : SVT_OCC32) : (cmax(W, H) >= 16 ? SVT_OCC16 : SVT_OCC8))) * 256 / NT,
+                    cmax(1, (228 * 1024) / (SMEM_BYTES + 1024 + 108 * NB)));
+    }
+    static constexpr int CTAS_PER_SM = ctas_per_sm(false);
 };
 
 struct QSet { int zbin, round, quant, qshift, dequant; };  // one of {DC, AC}
@@ -976,7 +988,7 @@ SVT_HD const int16_t* block_iscan(const KParams& p, const DevBlock& d) {
 #if defined(__CUDACC__)
 // FULL: 0 = switches read at run time (CfgRuntime); otherwise the CFG code of CfgFull
 template <int W, int H, bool QM, bool DIST, int FULL>
-__global__ void __launch_bounds__(Geo<W, H>::NT, Geo<W, H>::CTAS_PER_SM)
+__global__ void __launch_bounds__(Geo<W, H>::NT, Geo<W, H>::ctas_per_sm(QM || DIST))
 residual_kernel(const __grid_constant__ KParams p, int first_block, int count) {
     using G = Geo<W, H>;
     using C = typename std::conditional<FULL != 0, CfgFull<FULL>, CfgRuntime>::type;
