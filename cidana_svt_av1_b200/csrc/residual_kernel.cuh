@@ -881,11 +881,11 @@ SVT_HD void inv_col_k(const DevBlock& d, int c, const int* buf, PIX* pix, int pm
     const int* src = buf + (lr ? W - 1 - c : c);
     const Clamp k16(16);  // the column stage range: 16 bits for bd 8 / 10
     int x[H];
-#pragma unroll
     // already clamped to 16 bits by the row pass.  Rows >= KH (64-row sizes) hold the inverse row
     // transform of all-zero coefficient rows, i.e. zeros (EbTransforms.c:8299): they are neither
     // written by the row pass nor read here, and as compile-time zeros they fold the first stages
     // of the 64-point network away.
+#pragma unroll
     for (int r = 0; r < H; ++r) x[r] = r < G::KH ? src[r * G::LD] : 0;
     if constexpr (FAST) inv1d_k<H, KIND>(x, NoClamp());  // inside fast_limit: no clamp can bind
     else inv1d_k<H, KIND>(x, k16);
