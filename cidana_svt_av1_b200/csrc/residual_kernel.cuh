@@ -19,6 +19,7 @@
 #include <stddef.h>
 #include <stdint.h>
 #include <type_traits>
+#include <utility>
 #include "txfm1d.cuh"
 
 #if !defined(__CUDACC__)  // host emulation build (tests only): the two vector helpers used below
@@ -254,7 +255,10 @@ struct Geo {
     static constexpr int CTAS_PER_SM = ctas_per_sm(false);
 };
 
-struct QSet { int zbin, round, quant, qshift, dequant; };  // one of {DC, AC}
+// one of {DC, AC}.  Where the flat quantizer runs in its two-multiply form (two_mul below),
+// round / quant / qshift hold the pre-shifted terms 2 round, (quant + 2^16) << 15 and
+// quant_shift << (16 + log_scale) instead of the table values.
+struct QSet { int zbin, round, quant, qshift, dequant; };
 struct QRow { QSet dc, ac; };  // zbin / round already scaled by log_scale
 template <int NB>
 struct CtaShared {  // small per-CTA state next to the buffers above (108 bytes per block)
@@ -414,6 +418,20 @@ SVT_HD void inv1d_k(int (&x)[N], K k) {
     else identity<N>(x);
 }
 
+#if defined(__CUDA_ARCH__)
+template <int OFF>
+__device__ __forceinline__ int lds_s16_off(unsigned base) {
+    int v;
+    // volatile keeps it ordered against the barriers and the cp.async waits (all of them volatile asm
+    // or barrier intrinsics); no memory clobber, so ordinary loads and stores may still move past it
+    asm volatile("ld.shared.s16 %0, [%1+%2];" : "=r"(v) : "r"(base), "n"(OFF));
+    return v;
+}
+template <int STRIDE_BYTES, int N, int... R>
+__device__ __forceinline__ void lds_s16_col(unsigned base, int (&x)[N], std::integer_sequence<int, R...>) {
+    ((x[R] = lds_s16_off<R * STRIDE_BYTES>(base)), ...);
+}
+#endif
 // ---- phase 1: forward column transform, staged residual -> transpose buffer ------------------------
 // SRC8: `res` holds the 8-bit prediction block (W x H bytes) followed by the 8-bit source block
 // instead of an int16 residual (CfgFull::SRC_STAGED)
@@ -428,8 +446,15 @@ SVT_HD void fwd_col_k(const DevBlock& d, int c, int* buf, const int16_t* res) {
 #pragma unroll
         for (int r = 0; r < H; ++r) x[r] = (int(px[W * H + r * W + c]) - int(px[r * W + c])) * (1 << S0);
     } else {
+#if defined(__CUDA_ARCH__) && !defined(SVT_NO_LDS_S16)
+        // nvcc turns an int16 shared load into LDS.U16 + PRMT; ld.shared.s16 is one LDS.S16
+        lds_s16_col<W * 2>(unsigned(__cvta_generic_to_shared(res + c)), x, std::make_integer_sequence<int, H>());
+#pragma unroll
+        for (int r = 0; r < H; ++r) x[r] *= (1 << S0);  // rows already flipped
+#else
 #pragma unroll
         for (int r = 0; r < H; ++r) x[r] = int(res[r * W + c]) * (1 << S0);  // rows already flipped
+#endif
     }
     fwd1d_k<H, fwd_cos_col(W, H), KIND, (S1 > 0 ? S1 : 0)>(x);  // includes round_shift(., -shift[1])
     int* dst = buf + (lr ? W - 1 - c : c);  // flip left to right, EbTransforms.c:3752-3757
@@ -450,14 +475,45 @@ SVT_HD void phase_fwd_col(const DevBlock& d, int c, int* buf, const int16_t* res
 }
 
 // ---- quantizer for one coefficient ---------------------------------------------------------------
-template <int LOG_SCALE>
-SVT_HD QRow load_qrow(const int16_t* t) {
+// Two-multiply form of the flat quantizer: for log_scale < 2 and not in the kernels that also run
+// the qmatrix quantizer (which needs the table values) nor in the stand-alone slots (WIDE: their
+// callers hand in arbitrary rows).  -DSVT_QUANT_WIDE switches it off (A/B builds).
+SVT_HD constexpr bool two_mul(int log_scale, bool wide) {
+#if defined(SVT_QUANT_WIDE)
+    return false && log_scale < 2 && !wide;
+#else
+    return log_scale < 2 && !wide;
+#endif
+}
+// one table row (raw zbin / round / quant / quant_shift / dequant of one position class) -> QSet
+template <int LOG_SCALE, bool WIDE>
+SVT_HD QSet make_qset(int zbin, int round, int quant, int qshift, int dequant) {
     constexpr int rnd = LOG_SCALE ? (1 << (LOG_SCALE - 1)) : 0;
-    QRow q;
+    QSet e;
     // ROUND_POWER_OF_TWO(zbin / round, log_scale), EbFullLoop.c:246, :280
-    q.dc = QSet{ (int(t[0]) + rnd) >> LOG_SCALE, (int(t[8]) + rnd) >> LOG_SCALE, t[16], t[24], t[32] };
-    q.ac = QSet{ (int(t[1]) + rnd) >> LOG_SCALE, (int(t[9]) + rnd) >> LOG_SCALE, t[17], t[25], t[33] };
+    e.zbin = (zbin + rnd) >> LOG_SCALE;
+    e.round = (round + rnd) >> LOG_SCALE;
+    e.quant = quant; e.qshift = qshift; e.dequant = dequant;
+    if constexpr (two_mul(LOG_SCALE, WIDE)) {
+        e.round = int(uint32_t(e.round) << 1);
+        e.quant = int(uint32_t(quant + 65536) << 15);         // quant is an int16: 2^15 <= quant + 2^16 < 2^17
+        e.qshift = int(uint32_t(qshift) << (16 + LOG_SCALE));  // needs 0 <= quant_shift < 2^(16 - log_scale)
+    }
+    return e;
+}
+template <int LOG_SCALE, bool WIDE>
+SVT_HD QRow load_qrow(const int16_t* t) {
+    QRow q;
+    q.dc = make_qset<LOG_SCALE, WIDE>(t[0], t[8], t[16], t[24], t[32]);
+    q.ac = make_qset<LOG_SCALE, WIDE>(t[1], t[9], t[17], t[25], t[33]);
     return q;
+}
+SVT_HD uint32_t umulhi32(uint32_t a, uint32_t b) {
+#if defined(__CUDA_ARCH__)
+    return __umulhi(a, b);
+#else
+    return uint32_t((uint64_t(a) * b) >> 32);
+#endif
 }
 // flat (no qmatrix): aom_highbd_quantize_b*_avx2 arithmetic
 // (Source/Lib/Common/ASM_AVX2/highbd_quantize_intrin_avx2.c:80-125), equal to
@@ -466,16 +522,33 @@ SVT_HD QRow load_qrow(const int16_t* t) {
 // for the 8-bit C variant (EbFullLoop.c:86-88) and INT_MAX otherwise.  Returns |level|.
 // asum: running sum of |dqcoeff| (the bound that lets the inverse transform drop its clamps, see
 // fast_limit below)
-template <int LOG_SCALE>
+// WIDE: the 64-bit form for every log_scale (the stand-alone quantizer slots, whose callers hand
+// in their own table rows)
+template <int LOG_SCALE, bool WIDE = false>
 SVT_HD int quant_flat(int cf, const QSet& q, int t1max, int& qc, int& dqc, unsigned& asum) {
     const int sgn = (cf >> 31) | 1;
     const int ab = cf < 0 ? -cf : cf;
-    int t1 = ab + q.round;
-    t1 = t1 > t1max ? t1max : t1;
-    const int64_t p1 = int64_t(t1) * q.quant;
-    const uint32_t t2 = uint32_t(uint64_t(p1) >> 16) + uint32_t(t1);
-    const uint64_t p2 = uint64_t(t2) * uint32_t(q.qshift);
-    int aq = int(uint32_t(p2 >> (16 - LOG_SCALE)));
+    int aq;
+    constexpr bool kTwoMul = two_mul(LOG_SCALE, WIDE);
+    if constexpr (kTwoMul) {
+        // ((t1 * quant) >> 16) + t1 == (t1 * (quant + 2^16)) >> 16 == umulhi(2 t1, (quant + 2^16) << 15), and
+        // (t2 * quant_shift) >> (16 - log_scale) == umulhi(t2, quant_shift << (16 + log_scale)): two
+        // multiplies and no 64-bit shifts (17 -> 14 instructions per coefficient).  Exact for
+        // 0 <= t1 < 2^31 and 0 <= quant_shift < 2^(16 - log_scale); invert_quant produces
+        // quant_shift = 2^(16 - l) with l >= 2 (EbModeDecisionConfigurationProcess.c:322), and
+        // the table upload refuses anything else.
+        const uint32_t r2 = uint32_t(q.round);  // 2 round
+        const uint32_t t1x2 = t1max == 0x7fffffff ? (uint32_t(ab) << 1) + r2
+                                                  : uint32_t(ab + int(r2 >> 1) > t1max ? t1max : ab + int(r2 >> 1)) << 1;
+        aq = int(umulhi32(umulhi32(t1x2, uint32_t(q.quant)), uint32_t(q.qshift)));
+    } else {  // 64-point sizes: quant_shift << 18 can reach 2^32 (quant_shift = 2^14 at qindex 0)
+        int t1 = ab + q.round;
+        t1 = t1 > t1max ? t1max : t1;
+        const int64_t p1 = int64_t(t1) * q.quant;
+        const uint32_t t2 = uint32_t(uint64_t(p1) >> 16) + uint32_t(t1);
+        const uint64_t p2 = uint64_t(t2) * uint32_t(q.qshift);
+        aq = int(uint32_t(p2 >> (16 - LOG_SCALE)));
+    }
     aq = ab >= q.zbin ? aq : 0;
     qc = int(unsigned(aq) * unsigned(sgn));
     if constexpr (LOG_SCALE == 0) {
@@ -488,10 +561,10 @@ SVT_HD int quant_flat(int cf, const QSet& q, int t1max, int& qc, int& dqc, unsig
     }
     return aq;
 }
-template <int LOG_SCALE>
+template <int LOG_SCALE, bool WIDE = false>
 SVT_HD int quant_flat(int cf, const QSet& q, int t1max, int& qc, int& dqc) {
     unsigned unused = 0;
-    return quant_flat<LOG_SCALE>(cf, q, t1max, qc, dqc, unused);
+    return quant_flat<LOG_SCALE, WIDE>(cf, q, t1max, qc, dqc, unused);
 }
 // with quantization matrices: highbd_quantize_b_helper_c, EbFullLoop.c:239-296
 template <int LOG_SCALE>
@@ -544,9 +617,42 @@ SVT_HD constexpr unsigned fast_limit(bool bd10) {
 // the row's share of S goes back to it
 struct RowAux { unsigned sum = 0; int fast = 0; };
 
-// ---- phase 2: forward row -> (energy, pack) -> quantize -> inverse row, all on one thread's registers
-// isc: this block's iscan table (global memory).  Returns the row's eob candidate and
-// discarded-region energy.
+// ---- qcoeff / dqcoeff of 8- and 16-wide rows: 256-bit stores by the row owner ------------------------
+// sm_100 has 256-bit global stores (st.global.v8.b32 -> STG.E.ENL2.256): one full 32-byte sector
+// per thread and instruction.  In the flat kernels the owner of an 8- or 16-wide row stores its
+// q / dq row itself, eight coefficients at a time.  What it replaces: for 16-wide rows the
+// hand-over through shared memory described below (8 STS.128 + 8 LDS.128 + 4 warp syncs per
+// thread, a third of the 16x16 kernel's shared-memory wavefronts: 54.9 -> 53.3 us); for 8-wide
+// rows two 128-bit stores per array that each wrote HALF a sector (8x8: 51.5 -> 46.0 us -- partial
+// sector writes are what hurts: the same direct stores at 128 bits took the 32x32 kernel from
+// 39.6 to 59.0 us).  32-wide rows keep the hand-over: eight levels live next to the 32 dequantised
+// values spill in the 64-register kernels (44.1 vs 39.6 us).  Needs 32-byte aligned rows
+// (checked per block; 16-byte aligned rows take two 128-bit stores).
+#if !defined(SVT_NO_DIRECT256)
+#define SVT_DIRECT256 1
+#else
+#define SVT_DIRECT256 0
+#endif
+#if !defined(SVT_DIRECT256_MAXKW)
+#define SVT_DIRECT256_MAXKW 16  // 32-wide rows: eight levels live at once spill in the 64-register kernels (measured slower)
+#endif
+#if !defined(SVT_DIRECT256_MINKW)
+#define SVT_DIRECT256_MINKW 8
+#endif
+SVT_HD constexpr bool direct256(bool qm, int kw) { return SVT_DIRECT256 && !qm && kw >= SVT_DIRECT256_MINKW && kw <= SVT_DIRECT256_MAXKW; }
+SVT_HD void store8(int32_t* g, const int* v, bool al32) {
+#if defined(__CUDA_ARCH__)
+    if (al32) {
+        asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(g), "r"(v[0]), "r"(v[1]), "r"(v[2]),
+                     "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]) : "memory");
+        return;
+    }
+#else
+    (void)al32;
+#endif
+    *reinterpret_cast<int4*>(g) = make_int4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<int4*>(g + 4) = make_int4(v[4], v[5], v[6], v[7]);
+}
 // ---- qcoeff / dqcoeff leave the SM through the thread's own transpose-buffer row --------------------
 // A thread owns one row, so a direct store would have the 32 lanes of a warp write 16 bytes each
 // at a pitch of one row: 32 different cache lines per instruction, 8x the L1 wavefronts of a
@@ -670,6 +776,9 @@ SVT_HD void inv_row_store(int (&x)[W], int* row, bool bd10) {
     }
 }
 
+// ---- phase 2: forward row -> (energy, pack) -> quantize -> inverse row, all on one thread's registers
+// isc: this block's iscan table (global memory).  Returns the row's eob candidate and
+// discarded-region energy.
 // fast_flag: the block's shared "no clamp can bind" flag (written here, read by the column pass)
 template <int W, int H, int KIND, bool QM, bool DIST, class C = CfgRuntime>
 SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int* buf, const int16_t* isc,
@@ -750,7 +859,38 @@ SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int
                 *reinterpret_cast<uint32_t*>(q4) = 0u;
             }
         }
+        constexpr bool DIRECT = direct256(QM, KW);
         if (!use_qm) {
+            if constexpr (DIRECT) {
+                const bool al32 = !(((C::has_q(p) ? size_t(p.qcoeff) : 0) | (C::has_dq(p) ? size_t(p.dqcoeff) : 0) |
+                                     (size_t(d.coeff_off) * 4)) & 31);
+#pragma unroll
+                for (int c0 = 0; c0 < KW; c0 += 8) {
+                    int qv[8];
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        uint32_t lv4 = 0;
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const int c = c0 + 4 * h + j;
+                            int dqc;
+                            const int cf = x[c];
+                            const int aq = quant_flat<LS, QM>(cf, c == 0 ? q0 : qa, t1max, qv[4 * h + j], dqc, asum);
+                            if (lvrow) lv4 |= uint32_t(aq > 127 ? 127 : aq) << (8 * j);
+                            if constexpr (DIST) {
+                                const int dd = cf - dqc;
+                                dsum[0] += (unsigned long long)((long long)dd * dd);
+                                dsum[1] += (unsigned long long)((long long)cf * cf);
+                            }
+                            x[c] = dqc;
+                            last = aq != 0 ? c : last;
+                        }
+                        if (lvrow) *reinterpret_cast<uint32_t*>(lvrow + c0 + 4 * h) = lv4;
+                    }
+                    if (C::has_q(p)) store8(p.qcoeff + cbase + c0, qv, al32);
+                    if (C::has_dq(p)) store8(p.dqcoeff + cbase + c0, &x[c0], al32);
+                }
+            } else {
 #pragma unroll
             for (int c0 = 0; c0 < KW; c0 += 4) {
                 int qv[4];
@@ -760,7 +900,7 @@ SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int
                     const int c = c0 + j;
                     int dqc;
                     const int cf = x[c];
-                    const int aq = quant_flat<LS>(cf, c == 0 ? q0 : qa, t1max, qv[j], dqc, asum);
+                    const int aq = quant_flat<LS, QM>(cf, c == 0 ? q0 : qa, t1max, qv[j], dqc, asum);
                     if (lvrow) lv4 |= uint32_t(aq > 127 ? 127 : aq) << (8 * j);
                     if constexpr (DIST) {
                         const int dd = cf - dqc;
@@ -772,6 +912,7 @@ SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int
                 }
                 if (lvrow) *reinterpret_cast<uint32_t*>(lvrow + c0) = lv4;
                 emit_q<W, H, C>(p, row, cbase, c0, qv, x);
+            }
             }
         } else if constexpr (QM) {
             const int qmo = p.qm_off[((d.meta >> META_PLANE_SHIFT) & 3) > 0][G::TXS] + r * KW;
@@ -812,7 +953,7 @@ SVT_HD void row_k(const KParams& p, const DevBlock& d, const QRow& q, int r, int
             eob_max = 0;
         }
 #endif
-        flush_q<W, H, C>(p, d, r, row, x);
+        if constexpr (!direct256(QM, KW)) flush_q<W, H, C>(p, d, r, row, x);
     }
 
     if (C::stg(p) & STAGE_INV) {  // inv_txfm2d_add_c row pass, EbTransforms.c:8215-8236
@@ -1035,7 +1176,7 @@ residual_kernel(const __grid_constant__ KParams p, int first_block, int count) {
     auto fetch_qrows = [&] {
         if ((C::stg(p) & STAGE_QUANT) && mine)
             for (int own = own0; own < nb; own += OSTEP)
-                sh.q[own] = load_qrow<G::LOG_SCALE>(p.qtables + size_t(sh.blk[own].qrow) * 40);
+                sh.q[own] = load_qrow<G::LOG_SCALE, QM>(p.qtables + size_t(sh.blk[own].qrow) * 40);
     };
     TR();
     // copy teams: TPB consecutive threads move one block's rows, 16 bytes per thread per step;
@@ -1123,16 +1264,15 @@ template <int LOG_SCALE>
 __global__ void __launch_bounds__(256)
 quant_kernel(const int32_t* coeff, int n, const int16_t* tab /* 5 x {DC, AC} */,
              const int16_t* iscan, int32_t* qcoeff, int32_t* dqcoeff, uint16_t* eob) {
-    constexpr int rnd = LOG_SCALE ? (1 << (LOG_SCALE - 1)) : 0;
-    const QSet dc{ (int(tab[0]) + rnd) >> LOG_SCALE, (int(tab[2]) + rnd) >> LOG_SCALE, tab[4], tab[6], tab[8] };
-    const QSet ac{ (int(tab[1]) + rnd) >> LOG_SCALE, (int(tab[3]) + rnd) >> LOG_SCALE, tab[5], tab[7], tab[9] };
+    const QSet dc = make_qset<LOG_SCALE, true>(tab[0], tab[2], tab[4], tab[6], tab[8]);
+    const QSet ac = make_qset<LOG_SCALE, true>(tab[1], tab[3], tab[5], tab[7], tab[9]);
     __shared__ int s_eob;
     if (threadIdx.x == 0) s_eob = 0;
     __syncthreads();
     int e = 0;
     for (int i = threadIdx.x; i < n; i += blockDim.x) {
         int qc, dqc;
-        const int aq = quant_flat<LOG_SCALE>(coeff[i], i == 0 ? dc : ac, 0x7fffffff, qc, dqc);
+        const int aq = quant_flat<LOG_SCALE, true>(coeff[i], i == 0 ? dc : ac, 0x7fffffff, qc, dqc);
         qcoeff[i] = qc;
         dqcoeff[i] = dqc;
         if (aq != 0) { const int s = int(iscan[i]) + 1; e = s > e ? s : e; }

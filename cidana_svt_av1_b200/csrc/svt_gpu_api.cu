@@ -87,6 +87,18 @@ extern "C" void svtgpu_destroy(SvtGpuContext* c) {
 
 extern "C" int svtgpu_upload_quant_tables(SvtGpuContext* c, const int16_t* tables, int n_rows) {
     if (!c || !tables || n_rows <= 0) return SVTGPU_ERR_ARG;
+    // The fused kernels multiply by quant_shift << (16 + log_scale) (quant_flat): exact for
+    // 0 <= quant_shift < 2^15, which covers everything invert_quant can produce
+    // (1 << (16 - msb(d)) with d >= 4, EbModeDecisionConfigurationProcess.c:322-329).
+    for (int r = 0; r < n_rows; ++r)
+        for (int k = 0; k < 2; ++k)
+            if (tables[size_t(r) * 40 + 24 + k] < 0) {
+                char msg[160];
+                snprintf(msg, sizeof msg, "svtgpu_upload_quant_tables: row %d has a negative quant_shift (%d); "
+                         "av1_build_quantizer produces 1 << (16 - msb(q))", r, int(tables[size_t(r) * 40 + 24 + k]));
+                svtgpu_set_error("%s%s (line %d)", msg, "", __LINE__);
+                return SVTGPU_ERR_ARG;
+            }
     CK(cudaSetDevice(c->device));
     CK(cudaStreamSynchronize(c->stream));
     cudaFree(c->d_qtables);

@@ -67,7 +67,7 @@ SVT_HD constexpr int ilog2(int n) { int l = 0; while ((1 << l) < n) ++l; return 
 // half_btf with wrapping 32-bit arithmetic
 template <int BIT>
 SVT_HD int hb(int w0, int a, int w1, int b) {
-    const unsigned r = unsigned(w0) * unsigned(a) + unsigned(w1) * unsigned(b) + (1u << (BIT - 1));
+    const unsigned r = (unsigned(w0) * unsigned(a) + (1u << (BIT - 1))) + unsigned(w1) * unsigned(b);
     return int(r) >> BIT;
 }
 template <int BIT>
@@ -88,8 +88,8 @@ template <int BIT, int POST>
 SVT_HD int hbp(int w0, int a, int w1, int b) {
     if constexpr (POST == 0) return hb<BIT>(w0, a, w1, b);
     else {
-        const unsigned r = unsigned(w0) * unsigned(a) + unsigned(w1) * unsigned(b) +
-                           ((1u << (BIT - 1)) + (1u << (BIT + POST - 1)));
+        const unsigned r = (unsigned(w0) * unsigned(a) + ((1u << (BIT - 1)) + (1u << (BIT + POST - 1)))) +
+                           unsigned(w1) * unsigned(b);
         return int(r) >> (BIT + POST);
     }
 }

@@ -96,7 +96,11 @@ void svtgpu_destroy(SvtGpuContext *ctx);
 const char *svtgpu_last_error(void);
 
 /* tables[n_rows][5][8] int16: zbin, round, quant, quant_shift, dequant rows exactly as
- * av1_build_quantizer lays them out (EbModeDecisionConfigurationProcess.c:429; [0] DC, [1..7] AC) */
+ * av1_build_quantizer lays them out (EbModeDecisionConfigurationProcess.c:429; [0] DC, [1..7] AC).
+ * quant_shift must be non-negative, as invert_quant produces it (1 << (16 - msb), :322-329): the
+ * fused kernels multiply by quant_shift << (16 + log_scale).  A row that is not is refused with
+ * SVTGPU_ERR_ARG and the tables uploaded before stay in place.  (The stand-alone quantizer slots
+ * svtgpu_quantize_b* take their rows per call and accept any int16.) */
 int svtgpu_upload_quant_tables(SvtGpuContext *ctx, const int16_t *tables, int n_rows);
 /* wt/iwt: concatenated qmatrix arrays; off[plane>0][tx_size] = start of that size's matrix or -1
  * (what av1_qm_init binds into gqmatrix/giqmatrix, :524-554) */

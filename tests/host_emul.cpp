@@ -3,6 +3,7 @@
 // arithmetic can be checked against the oracle in the CPU-only test tier.  This is not a CPU
 // fallback: nothing in the product links or loads it.
 #include "../cidana_svt_av1_b200/csrc/host_plan.h"
+#include <random>
 #include <vector>
 using namespace svt;
 
@@ -30,7 +31,9 @@ static void run_size(const KParams& p, int first, int count) {
         int eob = 0;
         unsigned long long energy = 0;
         QRow q = {};
-        if (p.stages & STAGE_QUANT) q = load_qrow<G::LOG_SCALE>(p.qtables + size_t(d.qrow) * 40);
+        if (p.stages & STAGE_QUANT)  // the kernel instantiation that runs this batch: QM = (matrices uploaded and no dist)
+            q = (!p.dist && p.qm_wt) ? load_qrow<G::LOG_SCALE, true>(p.qtables + size_t(d.qrow) * 40)
+                                     : load_qrow<G::LOG_SCALE, false>(p.qtables + size_t(d.qrow) * 40);
         unsigned long long dist[2] = { 0, 0 };
         int fast_flag = 0;
         // The kernel decides per block, from S = sum |dqcoeff| (a warp-level reduction over the row
@@ -251,4 +254,40 @@ extern "C" int emul_clampfree_diff(int n, int kind, unsigned seed, int l1, int b
     return n == 8 ? clampfree_diff<8, 1>(seed, l1, bits, count) : clampfree_diff<16, 1>(seed, l1, bits, count);
 }
 extern "C" int emul_fast_e() { return kFastE; }
+
+// The two-multiply form of the flat quantizer (quant_flat) against its 64-bit form: every row of
+// `tables` (40 int16 each), DC and AC, log_scale 0 and 1, |coeff| over a dense low range, every
+// power of two +-1 and `n_random` random magnitudes below 2^limit_bits, both signs, both values
+// of the 16-bit clamp.  Returns the number of differing (level, dequantised value) pairs.
+template <int LS>
+static long long quant_forms_diff(const int16_t* tables, int n_rows, int limit_bits, int n_random, unsigned seed) {
+    long long bad = 0;
+    std::vector<int> mags;
+    for (int v = 0; v < 6000; ++v) mags.push_back(v);
+    for (int b = 12; b < limit_bits; ++b) for (int d = -2; d <= 2; ++d) mags.push_back((1 << b) + d);
+    std::mt19937 rng(seed);
+    for (int i = 0; i < n_random; ++i) mags.push_back(int(rng() & ((1u << limit_bits) - 1u)));
+    for (int r = 0; r < n_rows; ++r) {
+        const QRow q = load_qrow<LS, false>(tables + size_t(r) * 40), qw = load_qrow<LS, true>(tables + size_t(r) * 40);
+        for (int k = 0; k < 2; ++k) {
+            const QSet& e = k ? q.ac : q.dc;
+            const QSet& ew = k ? qw.ac : qw.dc;
+            for (int m : mags)
+                for (int sg = -1; sg <= 1; sg += 2)
+                    for (int t1max : { 32767, 0x7fffffff }) {
+                        int qa, da, qb, db;
+                        unsigned sa = 0, sb = 0;
+                        const int la = quant_flat<LS, false>(sg * m, e, t1max, qa, da, sa);
+                        const int lb = quant_flat<LS, true>(sg * m, ew, t1max, qb, db, sb);
+                        bad += la != lb || qa != qb || da != db || sa != sb;
+                    }
+        }
+    }
+    return bad;
+}
+extern "C" long long emul_quant_forms_diff(const int16_t* tables, int n_rows, int log_scale, int limit_bits,
+                                           int n_random, unsigned seed) {
+    return log_scale == 0 ? quant_forms_diff<0>(tables, n_rows, limit_bits, n_random, seed)
+                          : quant_forms_diff<1>(tables, n_rows, limit_bits, n_random, seed);
+}
 #endif  // EMUL_PART == 0

@@ -131,6 +131,21 @@ def test_qmatrix_blocks_without_an_upload_are_an_error():
         assert np.array_equal(out[k], want[k]), k
 
 
+def test_negative_quant_shift_is_refused_at_upload():
+    """The fused kernels multiply by quant_shift << (16 + log_scale); the upload refuses the one
+    thing that breaks it (a negative quant_shift, which av1_build_quantizer never produces)."""
+    t = tables(8).copy().reshape(-1, 40)
+    g = pkg.SvtGpu(0)
+    g.upload_quant_tables(t)
+    bad = t.copy()
+    bad[5, 25] = -3
+    with pytest.raises(pkg.SvtGpuError) as e:
+        g.upload_quant_tables(bad)
+    assert "quant_shift" in str(e.value)
+    batch = wl.make_frame_batch(128, 128, 1, 8, seed=2)
+    assert np.array_equal(g.run_host(batch)["eob"], checker(batch)["eob"])  # the earlier tables still serve
+
+
 def test_multi_device_handle_round_robins_pictures():
     """svtgpu_create_multi through the C ABI: every visible device (the same device twice on a
     one-GPU box, which exercises the same bookkeeping), pictures round-robin, outputs == checker."""

@@ -255,6 +255,21 @@ def test_clamp_free_inverse_equals_clamped_inside_the_limit():
     assert differs_beyond > 0
 
 
+def test_two_multiply_quantizer_equals_the_64_bit_form():
+    """quant_flat computes the level with two 32 x 32 -> high-word multiplies where log_scale < 2.
+    Checked against the 64-bit form it replaces on every row of the reference's tables (256 qindex
+    x 3 planes, both bit depths, DC and AC), a dense low range of magnitudes, every power of two
+    +-2 and random magnitudes below 2^30, both signs, with and without the 16-bit clamp."""
+    E = emul()
+    E.emul_quant_forms_diff.restype = ctypes.c_longlong
+    for bd in (8, 10):
+        t = np.ascontiguousarray(_tables(bd))
+        assert t.dtype == np.int16 and t.size % 40 == 0
+        for ls in (0, 1):
+            bad = E.emul_quant_forms_diff(t.ctypes.data_as(ctypes.c_void_p), t.size // 40, ls, 30, 3000, 7 + ls)
+            assert bad == 0, (bd, ls, bad)
+
+
 def test_both_inverse_paths_are_exercised():
     """The frame workloads run (almost) entirely inside fast_limit, the full-range sweep (almost)
     entirely outside: the emulation counts which inverse a block took."""
