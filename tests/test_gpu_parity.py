@@ -69,6 +69,19 @@ def test_ragged_tail_and_single_block():
     assert empty.n_blocks == 0
 
 
+@pytest.mark.parametrize("bd", [8, 10])
+def test_coefficient_rows_aligned_to_16_bytes_only(bd):
+    """coeff_off is promised to be a multiple of 4 coefficients, not 8: the 256-bit row stores of
+    the 8- and 16-wide sizes must fall back to 128-bit ones (store8), block by block -- here every
+    second block sits 16 bytes off a 32-byte boundary."""
+    base = wl.make_packed_batch(wl.valid_pairs(), bd, 9, seed=77 + bd)
+    blocks = base.blocks.copy()
+    blocks["coeff_off"] += (4 * (1 + (np.arange(len(blocks)) // 2))).astype(np.uint32)  # odd multiples of 4 for half of the blocks
+    assert (blocks["coeff_off"] % 8 == 4).any() and (blocks["coeff_off"] % 8 == 0).any()
+    batch = wl.Batch(blocks, base.residual, base.pred, base.n_coeff + 4 * (1 + len(blocks) // 2) + 4, bd, "odd")
+    check(run_gpu(batch), run_oracle(batch, tables(bd), load_scans(), threads=8), "16-byte rows")
+
+
 def test_clamp16_variant_8bit():
     pairs = [(s, 0) for s in range(19)]
     batch = wl.make_packed_batch(pairs, 8, 9, seed=3, qindex=(0, 1, 2), flags=wl.BLK_CLAMP16)
