@@ -20,6 +20,8 @@ name = sys.argv[1] if len(sys.argv) > 1 else "1080p8"
 dev = torch.device("cuda", 0)
 torch.cuda.set_device(dev)
 batch = bench.make_batch(name, 0, 1)
+if os.environ.get("TB_ALL_DCT"):  # every block DCT_DCT: what a kind-specialised launch would see
+    batch.blocks["tx_type"] = 0
 tables = bench.load_tables(batch.bd)
 g = pkg.SvtGpu(0)
 g.upload_quant_tables(tables)
