@@ -1217,12 +1217,42 @@ residual_kernel(const __grid_constant__ KParams p, int first_block, int count) {
             phase_row<W, H, QM, DIST, C>(p, sh.blk[b], sh.q[b], r, buf + b * G::BLK,
                                       block_iscan<W, H>(p, sh.blk[b]), e, en, ds, &sh.fast[b], aux, &sh.eob[b]);
             if (e) atomicMax(&sh.eob[b], e);  // (device: reduced inside row_k by shuffles, e == 0 here)
-            if (G::KW != W || G::KH != H) { if (en) atomicAdd(&sh.energy[b], en); }
+            if (G::KW != W || G::KH != H) {
+#if defined(__CUDA_ARCH__) && !defined(SVT_ENERGY_ATOMIC_PER_THREAD)
+                // a 64-bit shared-memory atomicAdd is a compare-and-swap loop: 64 row owners on one
+                // address serialise badly.  The rows of a block are LB consecutive lanes of one warp:
+                // sum there by shuffles, one atomic per group.
+                constexpr int LB = H < 32 ? H : 32;
+                const int lane = threadIdx.x & 31, li = r & (LB - 1);
+                const unsigned bmask = LB == 32 ? 0xffffffffu : (((1u << LB) - 1u) << (lane - li));
+#pragma unroll
+                for (int k = LB / 2; k > 0; k >>= 1) en += __shfl_xor_sync(bmask, en, k);
+                if (li == 0 && en) atomicAdd(&sh.energy[b], en);
+#else
+                if (en) atomicAdd(&sh.energy[b], en);
+#endif
+            }
             if constexpr (DIST) {
+#if defined(__CUDA_ARCH__) && !defined(SVT_ENERGY_ATOMIC_PER_THREAD)
+                // (rows >= KH of the 64-row sizes carry zeros here; every row owner takes part)
+                constexpr int LB = H < 32 ? H : 32;
+                const int lane = threadIdx.x & 31, li = r & (LB - 1);
+                const unsigned bmask = LB == 32 ? 0xffffffffu : (((1u << LB) - 1u) << (lane - li));
+#pragma unroll
+                for (int k = LB / 2; k > 0; k >>= 1) {
+                    ds[0] += __shfl_xor_sync(bmask, ds[0], k);
+                    ds[1] += __shfl_xor_sync(bmask, ds[1], k);
+                }
+                if (li == 0 && ds[1]) {
+                    atomicAdd(&sh.dist[b][0], ds[0]);
+                    atomicAdd(&sh.dist[b][1], ds[1]);
+                }
+#else
                 if (ds[1]) {
                     atomicAdd(&sh.dist[b][0], ds[0]);
                     atomicAdd(&sh.dist[b][1], ds[1]);
                 }
+#endif
             }
         }
     }

@@ -79,7 +79,14 @@ def test_coefficient_rows_aligned_to_16_bytes_only(bd):
     blocks["coeff_off"] += (4 * (1 + (np.arange(len(blocks)) // 2))).astype(np.uint32)  # odd multiples of 4 for half of the blocks
     assert (blocks["coeff_off"] % 8 == 4).any() and (blocks["coeff_off"] % 8 == 0).any()
     batch = wl.Batch(blocks, base.residual, base.pred, base.n_coeff + 4 * (1 + len(blocks) // 2) + 4, bd, "odd")
-    check(run_gpu(batch), run_oracle(batch, tables(bd), load_scans(), threads=8), "16-byte rows")
+    got, want = run_gpu(batch), run_oracle(batch, tables(bd), load_scans(), threads=8)
+    covered = np.zeros(batch.n_coeff, bool)  # the gaps between blocks belong to nobody: not compared
+    for off, s in zip(blocks["coeff_off"], blocks["tx_size"]):
+        covered[int(off):int(off) + max_eob(int(s))] = True
+    for k in ("qcoeff", "dqcoeff"):
+        assert np.array_equal(got[k][covered], want[k][covered]), k
+    for k in ("eob", "energy", "recon"):
+        assert np.array_equal(got[k], want[k]), k
 
 
 def test_clamp16_variant_8bit():
