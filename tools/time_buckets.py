@@ -20,6 +20,9 @@ name = sys.argv[1] if len(sys.argv) > 1 else "1080p8"
 dev = torch.device("cuda", 0)
 torch.cuda.set_device(dev)
 batch = bench.make_batch(name, 0, 1)
+if os.environ.get("TB_FRAC"):  # the first 1/k of the block list (first frames): buckets small enough to stay in L2 across repetitions
+    k = int(os.environ["TB_FRAC"])
+    batch = wl.Batch(batch.blocks[:len(batch.blocks) // k].copy(), batch.residual, batch.pred, batch.n_coeff, batch.bd, "frac")
 if os.environ.get("TB_ALL_DCT"):  # every block DCT_DCT: what a kind-specialised launch would see
     batch.blocks["tx_type"] = 0
 tables = bench.load_tables(batch.bd)
