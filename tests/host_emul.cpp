@@ -285,6 +285,52 @@ static long long quant_forms_diff(const int16_t* tables, int n_rows, int limit_b
     }
     return bad;
 }
+// quant_qm (two-multiply form below 2^21, 64-bit form above) against the reference's arithmetic
+// written out in 64 bits (highbd_quantize_b_helper_c, EbFullLoop.c:239-296), raw table rows.
+template <int LS>
+static long long quant_qm_diff(const int16_t* tables, int n_rows, int n_random, unsigned seed) {
+    long long bad = 0;
+    std::vector<int> mags;
+    for (int v = 0; v < 3000; ++v) mags.push_back(v);
+    for (int b = 12; b < 30; ++b) for (int d = -2; d <= 2; ++d) mags.push_back((1 << b) + d);
+    for (int d = -70000; d <= 70000; d += 4999) mags.push_back((1 << 21) + d);  // around the guard
+    std::mt19937 rng(seed);
+    for (int i = 0; i < n_random; ++i) mags.push_back(int(rng() & ((1u << 24) - 1u)));
+    const int wts[] = { 1, 7, 32, 33, 64, 127, 128, 200, 255 };
+    for (int r = 0; r < n_rows; r += 3) {
+        const QRow q = load_qrow<LS, true>(tables + size_t(r) * 40);
+        for (int k = 0; k < 2; ++k) {
+            const QSet& e = k ? q.ac : q.dc;
+            for (int m : mags)
+                for (int sg = -1; sg <= 1; sg += 2)
+                    for (int wt : wts) {
+                        const int iwt = 288 - wt > 255 ? 255 : (288 - wt < 1 ? 1 : 288 - wt);
+                        int qa, da;
+                        unsigned sa = 0;
+                        const int la = quant_qm<LS>(sg * m, e, wt, iwt, qa, da, sa);
+                        // the reference, 64-bit throughout
+                        const int cf = sg * m, sign = cf >> 31, ab = (cf ^ sign) - sign;
+                        const int cw = int(unsigned(cf) * unsigned(wt));
+                        int qb = 0, db = 0, lb = 0;
+                        if (cw >= e.zbin * 32 || cw <= -e.zbin * 32) {
+                            const int64_t tw = (int64_t(ab) + e.round) * wt;
+                            const int64_t t2 = ((tw * e.quant) >> 16) + tw;
+                            lb = int((t2 * e.qshift) >> (16 - LS + 5));
+                            const int dq = (e.dequant * iwt + 16) >> 5;
+                            const int adq = int(unsigned(lb) * unsigned(dq)) >> LS;
+                            qb = (lb ^ sign) - sign;
+                            db = (adq ^ sign) - sign;
+                        }
+                        bad += la != lb || qa != qb || da != db;
+                    }
+        }
+    }
+    return bad;
+}
+extern "C" long long emul_quant_qm_diff(const int16_t* tables, int n_rows, int log_scale, int n_random, unsigned seed) {
+    return log_scale == 0 ? quant_qm_diff<0>(tables, n_rows, n_random, seed)
+         : log_scale == 1 ? quant_qm_diff<1>(tables, n_rows, n_random, seed) : quant_qm_diff<2>(tables, n_rows, n_random, seed);
+}
 extern "C" long long emul_quant_forms_diff(const int16_t* tables, int n_rows, int log_scale, int limit_bits,
                                            int n_random, unsigned seed) {
     return log_scale == 0 ? quant_forms_diff<0>(tables, n_rows, limit_bits, n_random, seed)

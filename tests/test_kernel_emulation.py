@@ -270,6 +270,18 @@ def test_two_multiply_quantizer_equals_the_64_bit_form():
             assert bad == 0, (bd, ls, bad)
 
 
+def test_qmatrix_quantizer_equals_the_reference_arithmetic():
+    """quant_qm against highbd_quantize_b_helper_c's arithmetic written out in 64 bits, coefficient by
+    coefficient: a third of the table rows, nine weights, magnitudes up to 2^30, all three
+    log_scales.  (A two-multiply form guarded at 2^21 passed this test too but ran slower on B200 --
+    4k10qm 174 vs 183 Gcoeff/s, two code paths per coefficient -- and was dropped.)"""
+    E = emul()
+    E.emul_quant_qm_diff.restype = ctypes.c_longlong
+    t = np.ascontiguousarray(_tables(10))
+    for ls in (0, 1, 2):
+        assert E.emul_quant_qm_diff(t.ctypes.data_as(ctypes.c_void_p), t.size // 40, ls, 1500, 11 + ls) == 0, ls
+
+
 def test_both_inverse_paths_are_exercised():
     """The frame workloads run (almost) entirely inside fast_limit, the full-range sweep (almost)
     entirely outside: the emulation counts which inverse a block took."""
